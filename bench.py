@@ -1,0 +1,414 @@
+#!/usr/bin/env python
+"""Benchmark of the fused preprocessing path (BASELINE.json metric: preprocessed clips/s and
+% of HBM roofline, beside the CPU reference).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload NAME] [--impl b200|reference]
+
+A *step* is one pass of the hot path over one batch of synthetic uint8 clips: one
+``pva_preprocess`` call through the C ABI (one kernel launch per step).  Under torchrun every
+rank runs the same per-rank batch on its own GPU (weak scaling, no data-path collective --
+SURVEY.md section 8e); rank 0 prints ONE JSON line.
+
+Keys beyond the base contract:
+  roofline     dominant kernel: algorithmic bytes per launch / average launch duration
+               (CUDA events over the timed region) against MEASURED_PEAKS.json hbm_gbs
+  cpu_baseline the oracle's CPU pipeline (restated reference transform) on the host cores,
+               bounded sample, rank 0 at N=1 only
+  e2e          same metric through the public API with HOST buffers: pinned uint8 clips ->
+               H2D -> fused kernel -> D2H of [slow, fast] into pinned memory, every step
+
+``--impl reference`` times the reference's CPU implementation of the path (oracle port: the
+reference itself is pure Python over pytorchvideo, which is not installable here) on all host
+cores and prints the same line with ``"impl": "reference"``.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "preprocessed_clips_per_sec"
+UNIT = "clips/s"
+L2_BYTES = 126 * 1024 * 1024
+NOMINAL_HBM_GBS = 8000.0
+FALLBACK_HBM_GBS = 6650.0  # /opt/skills/guides/B200_PROFILING.md
+
+WORKLOADS = {
+    # BASELINE.json configs[1]: the configuration the metric is quoted on
+    "slowfast_train_b8": dict(batch=8, shape=(3, 64, 256, 340),
+                              kwargs=dict(num_frames=32, slowfast_alpha=4, training=True)),
+    # configs[0]
+    "slowfast_val_b8": dict(batch=8, shape=(3, 64, 256, 340),
+                            kwargs=dict(num_frames=32, slowfast_alpha=4, training=False)),
+    # configs[3]
+    "single_pathway_b64": dict(batch=64, shape=(3, 64, 256, 340),
+                               kwargs=dict(num_frames=16, crop_size=224, is_slowfast=False, training=True)),
+}
+
+
+# --------------------------------------------------------------------------------------
+# CPU arm (oracle port of the reference transform), duration-bounded, one process per core
+# --------------------------------------------------------------------------------------
+def _cpu_worker(widx, shape, kwargs, counter, go, stop):
+    import torch
+
+    from oracle import pipeline  # bench.py's cpu_baseline / reference arm may execute oracle/
+
+    torch.set_num_threads(1)  # what a DataLoader worker gets (torch/utils/data/_utils/worker.py)
+    torch.manual_seed(42 + widx)
+    g = torch.Generator().manual_seed(1234 + widx)
+    clip = torch.randint(0, 256, shape, dtype=torch.uint8, generator=g)
+    transform = pipeline.make_transform(**kwargs)
+    transform({"video": clip})  # warm the allocator
+    go.wait()
+    while not stop.is_set():
+        out = transform({"video": clip, "label": 0})
+        assert out["video"] is not None
+        with counter.get_lock():
+            counter.value += 1
+
+
+def cpu_reference_throughput(workload, seconds, warm_seconds=2.0, max_procs=64):
+    """clips/s of the reference CPU pipeline using one single-threaded process per host core."""
+    import multiprocessing as mp
+
+    ctx = mp.get_context("spawn")
+    try:
+        cores = len(os.sched_getaffinity(0))
+    except AttributeError:
+        cores = os.cpu_count() or 1
+    procs_n = max(1, min(cores, max_procs))
+    counter = ctx.Value("l", 0)
+    go, stop = ctx.Event(), ctx.Event()
+    wl = WORKLOADS[workload]
+    procs = [ctx.Process(target=_cpu_worker, args=(i, wl["shape"], wl["kwargs"], counter, go, stop), daemon=True)
+             for i in range(procs_n)]
+    for p in procs:
+        p.start()
+    time.sleep(0.5)
+    go.set()
+    # wait until every worker is warm: the counter starts moving
+    t_wait = time.time()
+    while counter.value < procs_n and time.time() - t_wait < 120:
+        time.sleep(0.05)
+    time.sleep(warm_seconds)
+    c0, t0 = counter.value, time.perf_counter()
+    time.sleep(seconds)
+    c1, t1 = counter.value, time.perf_counter()
+    stop.set()
+    for p in procs:
+        p.join(timeout=30)
+        if p.is_alive():
+            p.terminate()
+    clips = c1 - c0
+    return dict(value=clips / (t1 - t0), clips=clips, seconds=t1 - t0, cores=procs_n, host_cores=cores)
+
+
+def run_reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return  # other ranks exit 0 without work
+    wl = WORKLOADS[args.workload]
+    # a "step" is one batch of wl['batch'] clips; the run is duration-bounded so that it ends
+    # within minutes whatever K is
+    est = 10.0  # clips/s order of magnitude per core-second is ~10
+    want_clips = (args.steps + args.warmup) * wl["batch"]
+    seconds = max(5.0, min(40.0, want_clips / est))
+    r = cpu_reference_throughput(args.workload, seconds)
+    ms_per_step = 1000.0 * wl["batch"] / r["value"]
+    sample = (f"{r['clips']} clips of {wl['shape']} uint8 through oracle.pipeline.make_transform"
+              f"({wl['kwargs']}) in {r['seconds']:.1f}s on {r['cores']} single-thread processes")
+    line = {
+        "impl": "reference", "metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": args.workload, "batch_per_step": wl["batch"], "clip_shape": list(wl["shape"]),
+                   "transform": wl["kwargs"], "note": "duration-bounded sample; step = one batch equivalent"},
+        "cpu_baseline": {"value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": "port", "sample": sample},
+        "e2e": {"value": r["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# --------------------------------------------------------------------------------------
+# clocks
+# --------------------------------------------------------------------------------------
+_REASONS = {0x4: "sw_power_cap", 0x8: "hw_slowdown", 0x20: "sw_thermal_slowdown", 0x40: "hw_thermal_slowdown",
+            0x80: "hw_power_brake_slowdown", 0x2: "applications_clocks_setting", 0x10: "sync_boost"}
+
+
+class ClockSampler(threading.Thread):
+    """Samples SM clock and throttle reasons of one GPU through NVML while the timed region runs."""
+
+    def __init__(self, index, period=0.01):
+        super().__init__(daemon=True)
+        self.index, self.period = index, period
+        self.samples, self.reasons = [], set()
+        self.max_mhz = None
+        self._stop_evt = threading.Event()
+        self.ok = False
+        try:
+            import pynvml
+
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+            self.ok = True
+        except Exception:  # noqa: BLE001
+            self.ok = False
+
+    def run(self):
+        if not self.ok:
+            return
+        while not self._stop_evt.is_set():
+            try:
+                mhz = self.nv.nvmlDeviceGetClockInfo(self.h, self.nv.NVML_CLOCK_SM)
+                mask = self.nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                self.samples.append(mhz)
+                for bit, name in _REASONS.items():
+                    if mask & bit:
+                        self.reasons.add(name)
+            except Exception:  # noqa: BLE001
+                pass
+            time.sleep(self.period)
+
+    def finish(self):
+        self._stop_evt.set()
+        if self.is_alive():
+            self.join(timeout=2)
+        return {"sm_mhz": statistics.median(self.samples) if self.samples else None, "sm_max_mhz": self.max_mhz,
+                "reasons": sorted(self.reasons), "samples": len(self.samples)}
+
+
+def physical_gpu_index(local_rank):
+    vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+    if vis:
+        try:
+            return int(vis.split(",")[local_rank])
+        except (ValueError, IndexError):
+            return local_rank
+    return local_rank
+
+
+# --------------------------------------------------------------------------------------
+# B200 arm
+# --------------------------------------------------------------------------------------
+def measured_peak():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    try:
+        v = float(json.load(open(path))["hbm_gbs"])
+        return v, "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:  # noqa: BLE001
+        return FALLBACK_HBM_GBS, "fallback (B200_PROFILING.md)"
+
+
+def recorded_traffic(workload):
+    """DRAM bytes per launch of the dominant kernel from the committed ncu --set full capture."""
+    try:
+        return json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get(workload)
+    except Exception:  # noqa: BLE001
+        return None
+
+
+def run_b200_arm(args):
+    import torch
+
+    import pva_b200
+    from pva_b200 import _lib
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device (this path has no CPU fallback)")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+
+        dist.init_process_group("nccl", device_id=dev)
+
+    wl = WORKLOADS[args.workload]
+    B, shape, kw = wl["batch"], wl["shape"], wl["kwargs"]
+    t = pva_b200.make_transform(**kw, device=dev, out_dtype=torch.float16, channels_last=True,
+                                norm_mode=args.norm_mode, kernel=args.kernel)
+    esize = 2
+    C, crop, n_fast, n_slow = shape[0], t.crop_size, t.num_frames, t.n_slow
+
+    # ---- synthetic, device-resident, rotated so the working set exceeds L2 ----
+    in_bytes = B * int(torch.tensor(shape).prod())
+    out_bytes = B * C * (n_fast + n_slow) * crop * crop * esize
+    n_sets = max(4, -(-3 * L2_BYTES // (in_bytes + out_bytes)))
+    gen = torch.Generator().manual_seed(1234 + rank)
+    torch.manual_seed(42 + rank)
+    sets, algo_bytes = [], []
+    for s in range(n_sets):
+        clips = torch.randint(0, 256, (B,) + tuple(shape), dtype=torch.uint8, generator=gen).to(dev)
+        params = [t.sample_params(shape[2], shape[3]) for _ in range(B)]
+        sets.append(t.prepare_batch(clips, params))
+        b = 0
+        for p in params:
+            fh, fw = _lib.source_footprint(shape[2], shape[3], p.oh, p.ow, p.top, p.left, crop)
+            b += C * n_fast * fh * fw + C * (n_fast + n_slow) * crop * crop * esize
+        algo_bytes.append(b)
+    stream = torch.cuda.current_stream(dev)
+    raw_stream = stream.cuda_stream
+
+    def step(i):
+        sets[i % n_sets].launch_raw(raw_stream)
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+
+    sampler = ClockSampler(physical_gpu_index(local_rank))
+    for i in range(args.warmup):
+        step(i)
+    info = _lib.last_launch_info()
+    barrier()
+    sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    for i in range(args.steps):
+        step(args.warmup + i)
+    e1.record(stream)
+    barrier()
+    clocks = sampler.finish()
+    elapsed_ms = e0.elapsed_time(e1)
+    if dist is not None:
+        tt = torch.tensor([elapsed_ms], device=dev, dtype=torch.float64)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        elapsed_ms = float(tt.item())
+    ms_per_step = elapsed_ms / args.steps
+    value = world * B * args.steps / (elapsed_ms / 1000.0)
+    used = [(args.warmup + i) % n_sets for i in range(args.steps)]
+    mean_algo = sum(algo_bytes[u] for u in used) / len(used)
+
+    peak, peak_src = measured_peak()
+    achieved = mean_algo / (ms_per_step / 1000.0) / 1e9
+    traffic = recorded_traffic(args.workload)
+    roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                "traffic": traffic, "peak_source": peak_src, "frac_of_nominal_8TBs": achieved / NOMINAL_HBM_GBS,
+                "algorithmic_bytes_per_launch": mean_algo,
+                "kernel": {1: "pva_generic_kernel", 2: "pva_tiled_kernel"}.get(info["kernel"], "?")}
+
+    # ---- e2e: HOST buffers through the public API, copies inside the timed region ----------
+    e2e = run_e2e(torch, pva_b200, t, wl, dev, dist, world, rank, args)
+
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic",
+        "config": {"workload": args.workload, "batch_per_gpu": B, "global_batch": B * world,
+                   "clip_shape": list(shape), "transform": kw, "out": "fp16 THWC (channels_last_3d)",
+                   "norm_mode": args.norm_mode, "parallelism": f"dp{world} (clips sharded per rank, no collective)",
+                   "l2": f"{n_sets} rotating input/output sets = {(in_bytes + out_bytes) * n_sets >> 20} MiB > L2",
+                   "launch": info},
+        "roofline": roofline, "e2e": e2e, "gpu_launches": args.steps * info["launches"], "clocks": clocks,
+    }
+    if world == 1 and rank == 0 and not args.no_cpu_baseline:
+        del sets
+        torch.cuda.empty_cache()
+        r = cpu_reference_throughput(args.workload, args.cpu_seconds)
+        line["cpu_baseline"] = {
+            "value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": "port",
+            "sample": (f"{r['clips']} clips in {r['seconds']:.1f}s, oracle.pipeline.make_transform (restated "
+                       f"reference transform), {r['cores']} single-thread processes of {r['host_cores']} host cores")}
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    if dist is not None:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def run_e2e(torch, pva_b200, t, wl, dev, dist, world, rank, args):
+    """Public-API path with host buffers: SampleParams -> collate_raw_clips -> GpuPreprocess, then
+    the [slow, fast] result is read back into pinned host memory.  H2D and D2H are inside the
+    timed region, every step."""
+    B, shape = wl["batch"], wl["shape"]
+    steps = max(5, min(args.steps, args.e2e_steps))
+    gen = torch.Generator().manual_seed(99 + rank)
+    sp = pva_b200.SampleParams(t)
+    host_batches = []
+    for _ in range(2):
+        samples = [sp({"video": torch.randint(0, 256, shape, dtype=torch.uint8, generator=gen), "label": 0})
+                   for _ in range(B)]
+        b = pva_b200.collate_raw_clips(samples)
+        b["video"] = b["video"].pin_memory()
+        host_batches.append(b)
+    pre = pva_b200.GpuPreprocess(t, dev)
+    outs_host = None
+    h2d = host_batches[0]["video"].numel()
+    d2h = 0
+
+    def one(i):
+        nonlocal outs_host, d2h
+        batch = dict(host_batches[i % 2])
+        res = pre(batch)["video"]
+        res = res if isinstance(res, list) else [res]
+        # raw memory order (N, T, S, S, C): a flat copy on both sides
+        raws = [r.permute(0, 2, 3, 4, 1) for r in res]
+        if outs_host is None:
+            outs_host = [torch.empty(r.shape, dtype=r.dtype, pin_memory=True) for r in raws]
+            d2h = sum(r.numel() * r.element_size() for r in raws)
+        for h, r in zip(outs_host, raws):
+            h.copy_(r, non_blocking=True)
+
+    for i in range(3):
+        one(i)
+    if dist is not None:
+        dist.barrier()
+    torch.cuda.synchronize(dev)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0 = time.perf_counter()
+    e0.record()
+    for i in range(steps):
+        one(i)
+    e1.record()
+    torch.cuda.synchronize(dev)
+    wall_ms = (time.perf_counter() - t0) * 1000.0
+    ms = max(e0.elapsed_time(e1), wall_ms)
+    if dist is not None:
+        tt = torch.tensor([ms], device=dev, dtype=torch.float64)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        ms = float(tt.item())
+    return {"value": world * B * steps / (ms / 1000.0), "unit": UNIT, "h2d_bytes_per_step": int(h2d),
+            "d2h_bytes_per_step": int(d2h), "steps": steps, "ms_per_step": ms / steps,
+            "path": "SampleParams -> collate_raw_clips (pinned) -> GpuPreprocess -> D2H of [slow, fast] (pinned)"}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5000)
+    ap.add_argument("--warmup", type=int, default=50)
+    ap.add_argument("--impl", choices=["b200", "reference"], default="b200")
+    ap.add_argument("--workload", choices=sorted(WORKLOADS), default="slowfast_train_b8")
+    ap.add_argument("--norm-mode", dest="norm_mode", choices=["affine", "exact"], default="affine")
+    ap.add_argument("--kernel", choices=["auto", "generic", "tiled"], default="auto")
+    ap.add_argument("--e2e-steps", dest="e2e_steps", type=int, default=40)
+    ap.add_argument("--cpu-seconds", dest="cpu_seconds", type=float, default=12.0)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.warmup < 3:
+        args.warmup = 3  # timing rule: at least 3 warm-up steps
+    if args.impl == "reference":
+        run_reference_arm(args)
+    else:
+        run_b200_arm(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,268 @@
+"""Parity of the CUDA path (through the C ABI) against the oracle.  Needs a B200: -m gpu.
+
+Tolerances (BASELINE.json north_star):
+  * geometry -- temporal indices, crop window, flip, pathway packing: bit-exact
+  * fp32 output, EXACT normalisation: bit-identical to the C restatement of ATen's arithmetic
+  * fp32 output, AFFINE normalisation (production default): <= 4e-6 absolute of the oracle
+  * fp16 output: <= 1e-3 absolute of the fp32 oracle
+  * bf16 output: within one bf16 ulp of oracle.bfloat16() (1e-3 absolute is unreachable in bf16)
+"""
+import hashlib
+
+import numpy as np
+import pytest
+import torch
+
+import pva_b200
+from oracle import pipeline
+from pva_b200 import _lib
+from pva_b200.geometry import ClipParams
+
+from _util import (c_oracle_explicit, draws_for_case, full_kwargs, load_large, load_small, oracle_explicit,
+                   synth_clip)
+
+pytestmark = pytest.mark.gpu
+
+META, DATA = load_small()
+KERNELS = ["generic", "tiled"]
+FP16_TOL = 1e-3
+AFFINE_FP32_TOL = 4e-6
+
+
+def params_from_draws(draws, h, w):
+    size, top, left, flip = draws
+    oh, ow = pipeline.resized_hw(h, w, size)
+    return ClipParams(size, oh, ow, top, left, flip)
+
+
+def gpu_run(clip, draws, kw, **opts):
+    t = pva_b200.make_transform(**kw, **opts)
+    p = params_from_draws(draws, clip.shape[2], clip.shape[3])
+    out = t.explicit(clip.cuda(), p)
+    torch.cuda.synchronize()
+    out = out if isinstance(out, list) else [out]
+    return [o.float().cpu().contiguous().numpy() for o in out], _lib.last_launch_info()
+
+
+def supported(kernel, fn):
+    """Run fn; a forced tiled kernel may legitimately refuse a shape (NotImplementedError)."""
+    try:
+        return fn()
+    except NotImplementedError as e:
+        if kernel == "tiled":
+            pytest.skip(f"tiled kernel declines this shape: {e}")
+        raise
+
+
+@pytest.mark.parametrize("kernel", KERNELS)
+@pytest.mark.parametrize("name", sorted(META))
+def test_golden_small_fp32_exact(name, kernel, cuda_device):
+    m = META[name]
+    kw = full_kwargs(m["kwargs"])
+    clip = torch.from_numpy(DATA[f"{name}/in"])
+    draws = draws_for_case(kw, m["shape"][2], m["shape"][3], m["seed"])
+    outs, info = supported(kernel, lambda: gpu_run(clip, draws, kw, out_dtype=torch.float32, channels_last=False,
+                                                   norm_mode="exact", kernel=kernel))
+    c_ref = c_oracle_explicit(clip, draws, kw)
+    for i, (o, c) in enumerate(zip(outs, c_ref)):
+        assert np.array_equal(o, c), f"out{i}: CUDA differs from the C restatement"
+        # reference's own output: ATen's small-frame path may differ by an ulp
+        assert np.abs(o - DATA[f"{name}/out{i}"]).max() <= 1e-6
+
+
+@pytest.mark.parametrize("kernel", KERNELS)
+@pytest.mark.parametrize("name", sorted(load_large()))
+def test_golden_large_fp32_exact_is_bit_identical_to_reference(name, kernel, cuda_device):
+    e = load_large()[name]
+    kw = full_kwargs(e["kwargs"])
+    clip = synth_clip(e["shape"], e["seed"])
+    draws = draws_for_case(kw, e["shape"][2], e["shape"][3], e["seed"])
+    outs, info = supported(kernel, lambda: gpu_run(clip, draws, kw, out_dtype=torch.float32, channels_last=False,
+                                                   norm_mode="exact", kernel=kernel))
+    for o, g in zip(outs, e["outs"]):
+        assert list(o.shape) == g["shape"]
+        assert hashlib.sha256(o.tobytes()).hexdigest() == g["sha256"]
+
+
+@pytest.mark.parametrize("kernel", KERNELS)
+@pytest.mark.parametrize("channels_last", [False, True])
+@pytest.mark.parametrize("name", ["train_256x340", "val_256x340", "train_single_224"])
+def test_production_modes_within_tolerance(name, channels_last, kernel, cuda_device):
+    e = load_large()[name]
+    kw = full_kwargs(e["kwargs"])
+    clip = synth_clip(e["shape"], e["seed"])
+    draws = draws_for_case(kw, e["shape"][2], e["shape"][3], e["seed"])
+    ref = c_oracle_explicit(clip, draws, kw)  # == reference bit for bit (test above)
+    run = lambda **o: supported(kernel, lambda: gpu_run(clip, draws, kw, channels_last=channels_last, kernel=kernel, **o))[0]
+    for o, r in zip(run(out_dtype=torch.float32, norm_mode="affine"), ref):
+        assert np.abs(o - r).max() <= AFFINE_FP32_TOL
+    for o, r in zip(run(out_dtype=torch.float16, norm_mode="affine"), ref):
+        assert np.abs(o - r).max() <= FP16_TOL
+    for o, r in zip(run(out_dtype=torch.float16, norm_mode="exact"), ref):
+        assert np.array_equal(o, torch.from_numpy(r).half().float().numpy())  # == oracle.half() exactly
+    for o, r in zip(run(out_dtype=torch.bfloat16, norm_mode="affine"), ref):
+        rb = torch.from_numpy(r).bfloat16().float().numpy()
+        ulp = np.maximum(np.abs(rb), 2.0 ** -126) * 2.0 ** -7
+        assert (np.abs(o - rb) <= ulp).all()
+
+
+def encoded_clip(kind, c, t, h, w):
+    """uint8 clip whose value encodes one coordinate, so geometry can be decoded exactly."""
+    clip = torch.zeros((c, t, h, w), dtype=torch.uint8)
+    if kind == "frame":
+        clip += torch.arange(t, dtype=torch.uint8).view(1, t, 1, 1)
+    elif kind == "row":
+        clip += (torch.arange(h) % 256).to(torch.uint8).view(1, 1, h, 1)
+    elif kind == "col":
+        clip += (torch.arange(w) % 256).to(torch.uint8).view(1, 1, 1, w)
+    elif kind == "chan":
+        clip += (torch.arange(c) * 50).to(torch.uint8).view(c, 1, 1, 1)
+    return clip
+
+
+@pytest.mark.parametrize("kernel", KERNELS)
+@pytest.mark.parametrize("flip", [False, True])
+def test_geometry_is_bit_exact_with_index_encoded_clips(flip, kernel, cuda_device):
+    """Identity scale (size == short side) makes every output a pure lookup lut[src], so the
+    source frame / row / column / channel of every output element can be read back exactly."""
+    c, t, h, w, crop, nf, alpha = 3, 64, 256, 340, 224, 32, 4
+    kw = full_kwargs(dict(num_frames=nf, crop_size=crop, slowfast_alpha=alpha))
+    top, left = 17, 93
+    draws = (256, top, left, flip)
+    lut = torch.from_numpy(np.asarray(__import__("oracle.c_oracle", fromlist=["x"]).build_lut(kw["mean"], kw["std"])))
+    idx1 = list(pva_b200.temporal_indices(t, nf))
+    idx2 = list(pva_b200.pack_indices(nf, alpha))
+    for kind in ["frame", "row", "col", "chan"]:
+        clip = encoded_clip(kind, c, t, h, w)
+        (slow, fast), _ = supported(kernel, lambda: gpu_run(clip, draws, kw, out_dtype=torch.float32,
+                                                            channels_last=True, norm_mode="exact", kernel=kernel))
+        cols = [left + (crop - 1 - x if flip else x) for x in range(crop)]
+        want = torch.empty(c, nf, crop, crop)
+        for ci in range(c):
+            for k in range(nf):
+                if kind == "frame":
+                    want[ci, k] = lut[ci, idx1[k]]
+                elif kind == "row":
+                    want[ci, k] = lut[ci, [(top + y) % 256 for y in range(crop)]].view(crop, 1).expand(crop, crop)
+                elif kind == "col":
+                    want[ci, k] = lut[ci, [cc % 256 for cc in cols]].view(1, crop).expand(crop, crop)
+                else:
+                    want[ci, k] = lut[ci, ci * 50]
+        assert np.array_equal(fast, want.numpy()), kind
+        assert np.array_equal(slow, want[:, idx2].numpy()), kind
+
+
+@pytest.mark.parametrize("kernel", KERNELS)
+def test_ragged_batch_matches_per_clip_oracle(kernel, cuda_device):
+    """Clips of different T, H, W and orientation in one call, batch outputs stacked like default_collate."""
+    kw = full_kwargs(dict(num_frames=8, crop_size=128, slowfast_alpha=4, min_short_side_scale=128,
+                          max_short_side_scale=160, training=True))
+    shapes = [(3, 16, 128, 172), (3, 21, 172, 128), (3, 8, 144, 192), (3, 30, 130, 131), (3, 9, 128, 128)]
+    t = pva_b200.make_transform(**kw, out_dtype=torch.float32, channels_last=True, norm_mode="exact", kernel=kernel)
+    torch.manual_seed(1234)
+    clips, params, draws = [], [], []
+    for i, s in enumerate(shapes):
+        clips.append(synth_clip(s, 200 + i))
+        d = pipeline.replay_draws(s[2], s[3], 128, 160, 128, 0.5)
+        draws.append(d)
+        params.append(params_from_draws(d, s[2], s[3]))
+    slow, fast = supported(kernel, lambda: t.run_batch([c.cuda() for c in clips], params))
+    torch.cuda.synchronize()
+    assert slow.shape == (5, 3, 2, 128, 128) and fast.shape == (5, 3, 8, 128, 128)
+    assert fast.is_contiguous(memory_format=torch.channels_last_3d)
+    for i, (clip, d) in enumerate(zip(clips, draws)):
+        rs, rf = c_oracle_explicit(clip, d, kw)
+        assert np.array_equal(fast[i].cpu().contiguous().numpy(), rf)
+        assert np.array_equal(slow[i].cpu().contiguous().numpy(), rs)
+
+
+@pytest.mark.parametrize("kernel", KERNELS)
+def test_config1_full_size_val_batch(kernel, cuda_device):
+    """BASELINE.json configs[0]: 8 synthetic uint8 64x256x340 clips through the SlowFast val transform;
+    fp16 channels-last outputs checked against the CPU oracle on every element."""
+    kw = full_kwargs({})
+    t = pva_b200.make_transform(**kw, kernel=kernel)
+    clips = torch.stack([synth_clip((3, 64, 256, 340), 1234 + i) for i in range(8)])
+    p = t.sample_params(256, 340)
+    assert (p.oh, p.ow, p.top, p.left, p.flip) == (256, 340, 0, 42, False)
+    slow, fast = supported(kernel, lambda: t.run_batch(clips.cuda(), [p] * 8))
+    torch.cuda.synchronize()
+    assert slow.shape == (8, 3, 8, 256, 256) and fast.shape == (8, 3, 32, 256, 256)
+    assert slow.dtype == torch.float16 and fast.is_contiguous(memory_format=torch.channels_last_3d)
+    for i in range(8):
+        rs, rf = c_oracle_explicit(clips[i], (256, 0, 42, False), kw)
+        assert np.abs(fast[i].float().cpu().numpy() - rf).max() <= FP16_TOL
+        assert np.abs(slow[i].float().cpu().numpy() - rs).max() <= FP16_TOL
+
+
+@pytest.mark.parametrize("kernel", KERNELS)
+def test_full_size_train_batch_properties(kernel, cuda_device):
+    """BASELINE.json configs[1] at full size, through size-independent properties:
+    slow == fast[idx2]; flipping mirrors the output; a clip's result does not depend on its
+    batch neighbours; repeated calls are identical."""
+    kw = full_kwargs(dict(training=True))
+    t = pva_b200.make_transform(**kw, kernel=kernel)
+    clips = torch.stack([synth_clip((3, 64, 256, 340), 4321 + i) for i in range(8)]).cuda()
+    torch.manual_seed(42)
+    params = [t.sample_params(256, 340) for _ in range(8)]
+    slow, fast = supported(kernel, lambda: t.run_batch(clips, params))
+    idx2 = torch.tensor(pva_b200.pack_indices(32, 4), device="cuda")
+    assert torch.equal(slow, fast.index_select(2, idx2))
+    slow2, fast2 = t.run_batch(clips, params)
+    assert torch.equal(fast, fast2) and torch.equal(slow, slow2)
+    flipped = [ClipParams(p.size, p.oh, p.ow, p.top, p.left, not p.flip) for p in params]
+    _, fast_f = t.run_batch(clips, flipped)
+    assert torch.equal(fast_f, fast.flip(-1))
+    _, single = t.run_batch(clips[3:4], params[3:4])
+    assert torch.equal(single[0], fast[3])
+    # spot-check two clips on every element against the oracle
+    for i in (0, 5):
+        p = params[i]
+        rs, rf = c_oracle_explicit(clips[i].cpu(), (p.size, p.top, p.left, p.flip), kw)
+        assert np.abs(fast[i].float().cpu().numpy() - rf).max() <= FP16_TOL
+
+
+def test_dict_contract_and_seeded_draws(cuda_device):
+    """make_transform(...)(sample) behaves like the reference Compose: same dict object back,
+    'audio' removed, other keys kept, [slow, fast] order, and a seeded call makes the reference's draws."""
+    kw = dict(min_short_side_scale=128, max_short_side_scale=160, crop_size=128, num_frames=8, training=True)
+    clip = synth_clip((3, 16, 128, 170), 5)
+    t = pva_b200.make_transform(**kw, out_dtype=torch.float32, norm_mode="exact")
+    sample = {"video": clip.clone(), "audio": torch.zeros(3), "label": 4, "video_name": "x"}
+    torch.manual_seed(77)
+    out = t(sample)
+    assert out is sample and "audio" not in out and out["label"] == 4 and out["video_name"] == "x"
+    slow, fast = out["video"]
+    assert slow.shape == (3, 2, 128, 128) and fast.shape == (3, 8, 128, 128) and fast.is_cuda
+    torch.manual_seed(77)
+    ref = pipeline.make_transform(**kw)({"video": clip.clone()})["video"]
+    # ATen CPU dispatch may wobble by an ulp at this frame size
+    assert np.abs(fast.cpu().numpy() - ref[1].numpy()).max() <= 1e-6 and np.abs(slow.cpu().numpy() - ref[0].numpy()).max() <= 1e-6
+    single = pva_b200.make_transform(is_slowfast=False, num_frames=4, crop_size=64, min_short_side_scale=64)(
+        {"video": synth_clip((3, 8, 64, 80), 1)})["video"]
+    assert isinstance(single, torch.Tensor) and single.shape == (3, 4, 64, 64)
+
+
+def test_batched_handover_matches_per_clip_transform(cuda_device):
+    kw = dict(min_short_side_scale=128, max_short_side_scale=160, crop_size=128, num_frames=8, training=True)
+    t = pva_b200.make_transform(**kw)
+    for on_worker in (False, True):
+        sp = pva_b200.SampleParams(t, subsample_on_worker=on_worker)
+        torch.manual_seed(11)
+        samples = [sp({"video": synth_clip((3, 16, 128, 170), 30 + i), "label": i}) for i in range(4)]
+        batch = pva_b200.GpuPreprocess(t)(pva_b200.collate_raw_clips(samples))
+        slow, fast = batch["video"]
+        assert batch["label"].tolist() == [0, 1, 2, 3] and "pva_params" not in batch
+        torch.manual_seed(11)
+        for i in range(4):
+            s, f = t({"video": synth_clip((3, 16, 128, 170), 30 + i)})["video"]
+            assert torch.equal(f, fast[i]) and torch.equal(s, slow[i])
+
+
+def test_errors_raise_reference_exception_types(cuda_device):
+    t = pva_b200.make_transform(min_short_side_scale=16, crop_size=32)
+    with pytest.raises(ValueError, match="larger than input image size"):
+        t({"video": torch.zeros(3, 8, 40, 60, dtype=torch.uint8, device="cuda")})
+    with pytest.raises(ValueError, match="crop window"):
+        pva_b200.make_transform(crop_size=32, num_frames=4).run_batch(
+            [torch.zeros(3, 8, 40, 60, dtype=torch.uint8, device="cuda")], [ClipParams(40, 40, 60, 20, 0, False)])
