@@ -225,7 +225,11 @@ int pva_preprocess(const PvaClipDesc* clips, int32_t n_clips, const PvaPlan* pla
             g_info.rows_per_tile = 0;
             g_info.tiles += grid;
         }
-        if (ce != cudaSuccess) return fail(PVA_ERR_CUDA, "kernel launch failed: %s", cudaGetErrorString(ce));
+        if (ce != cudaSuccess) {
+            (void)cudaGetLastError();  // do not leave the error for an unrelated later call to trip over
+            return fail(PVA_ERR_CUDA, "%s kernel launch failed: %s", use_tiled ? "tiled" : "generic",
+                        cudaGetErrorString(ce));
+        }
         g_info.launches += 1;
         done += n;
     }

@@ -29,7 +29,7 @@ __global__ void __launch_bounds__(256) pva_generic_kernel(const __grid_constant_
     int y0, y1, x0, x1;
     float ly0, ly1, lx0, lx1;
     bilinear_taps(g.sy, g.top + y, g.h, y0, y1, ly0, ly1);
-    const int col = g.left + (g.flip ? crop - 1 - x : x);
+    const int col = g.left + ((g.flip & 1) ? crop - 1 - x : x);
     bilinear_taps(g.sx, col, g.w, x0, x1, lx0, lx1);
 
     const int t_src = p.frame_idx[g.idx_row][k];
