@@ -268,21 +268,46 @@ def run_b200_arm(args):
     def step(i):
         sets[i % n_sets].launch_raw(raw_stream)
 
+    graph = None
+    if args.graph:
+        # one CUDA graph replays a full rotation over the buffer sets: n_sets launches per replay
+        for i in range(n_sets):
+            step(i)
+        torch.cuda.synchronize(dev)
+        cap = torch.cuda.Stream(dev)
+        with torch.cuda.stream(cap):
+            graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(graph, stream=cap):
+                for i in range(n_sets):
+                    sets[i].launch_raw(cap.cuda_stream)
+        torch.cuda.synchronize(dev)
+        if args.steps % n_sets or args.warmup % n_sets:
+            args.steps = max(n_sets, args.steps // n_sets * n_sets)
+            args.warmup = max(n_sets, -(-args.warmup // n_sets) * n_sets)
+
     def barrier():
         if dist is not None:
             dist.barrier()
         torch.cuda.synchronize(dev)
 
     sampler = ClockSampler(physical_gpu_index(local_rank))
-    for i in range(args.warmup):
-        step(i)
+    if graph is not None:
+        for _ in range(args.warmup // n_sets):
+            graph.replay()
+    else:
+        for i in range(args.warmup):
+            step(i)
     info = _lib.last_launch_info()
     barrier()
     sampler.start()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record(stream)
-    for i in range(args.steps):
-        step(args.warmup + i)
+    if graph is not None:
+        for _ in range(args.steps // n_sets):
+            graph.replay()
+    else:
+        for i in range(args.steps):
+            step(args.warmup + i)
     e1.record(stream)
     barrier()
     clocks = sampler.finish()
@@ -315,7 +340,7 @@ def run_b200_arm(args):
                    "clip_shape": list(shape), "transform": kw, "out": "fp16 THWC (channels_last_3d)",
                    "norm_mode": args.norm_mode, "parallelism": f"dp{world} (clips sharded per rank, no collective)",
                    "l2": f"{n_sets} rotating input/output sets = {(in_bytes + out_bytes) * n_sets >> 20} MiB > L2",
-                   "launch": info},
+                   "launch": info, "cuda_graph": bool(args.graph)},
         "roofline": roofline, "e2e": e2e, "gpu_launches": args.steps * info["launches"], "clocks": clocks,
     }
     if world == 1 and rank == 0 and not args.no_cpu_baseline:
@@ -401,6 +426,7 @@ def main():
     ap.add_argument("--e2e-steps", dest="e2e_steps", type=int, default=40)
     ap.add_argument("--cpu-seconds", dest="cpu_seconds", type=float, default=12.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--graph", action="store_true", help="replay the steps from a captured CUDA graph")
     args = ap.parse_args()
     if args.warmup < 3:
         args.warmup = 3  # timing rule: at least 3 warm-up steps

@@ -2,12 +2,17 @@
 //
 // Work item ("tile") = (clip, fast frame k, band of R output rows), all C=3 channels.
 // Per tile:
-//   producer warp  : cp.async.bulk (TMA, 1-D) of the source row segments the band touches,
-//                    three planes, into a shared-memory stage; completion on an mbarrier.
-//                    Temporal subsampling (run.py:82) is folded into the source address.
+//   producer warp  : 128-bit cp.async (LDGSTS) of the source row segments the band touches,
+//                    three planes, into a shared-memory stage; completion on an mbarrier
+//                    (cp.async.mbarrier.arrive).  Per-row cp.async.bulk copies were measured at
+//                    ~90 cycles per 256-byte row on the SM's TMA unit -- 57 us for the loads
+//                    alone -- so the row segments go through LDGSTS and TMA is kept for the
+//                    large contiguous stores.  Temporal subsampling (run.py:82) is folded into
+//                    the source address.
 //   consumer warps : each thread owns 4 adjacent output columns x 3 channels.  The x-pass is
 //                    computed once per SOURCE row (two aligned 32-bit shared loads per plane,
-//                    taps picked with PRMT) and kept in registers; consecutive output rows
+//                    taps picked with PRMT, bytes turned into floats as fp16 subnormals: a
+//                    zero-extended byte IS the half b * 2^-24) and kept in registers; consecutive output rows
 //                    reuse it for the y-pass (bilinear, run.py:89/95).  Crop and flip
 //                    (run.py:90-91) are folded into the per-thread column tables, Div255 +
 //                    Normalize (run.py:83-84) into the epilogue (AFFINE) or a table (EXACT).
@@ -17,8 +22,15 @@
 //                    (PackPathway, run.py:59-63) -- the source is read once.
 //
 // The source row pitch (340 B) is not a multiple of 16, so a 2-D tensor map is not legal; each
-// row segment is copied from its 16-byte-aligned superset and the consumers add the per-row
-// shift.  The library only ever reads 16-byte granules that contain at least one byte of the clip.
+// row segment is copied from its 16-byte-aligned superset.  The staged pitch is chosen congruent
+// to the source pitch modulo 16, which makes the staged address of (row, column) LINEAR in the
+// row index although every row starts at a different 16-byte phase: no per-row shift to compute.
+// The library only ever reads 16-byte granules that contain at least one byte of the clip.
+//
+// Layout: this kernel writes T x S x S x C (channels-last) only; the reference's C x T x S x S
+// order is served by the generic kernel.
+#include <stdlib.h>
+
 #include <type_traits>
 
 #include "pva_kernels.cuh"
@@ -27,9 +39,10 @@ namespace pva {
 
 namespace {
 
-constexpr int kConsumerThreads = 256;
+constexpr int kConsumerThreads = 512;
 constexpr int kBlockThreads = kConsumerThreads + 32;
-constexpr int kStages = 3;
+constexpr int kMaxStages = 3;
+constexpr int kMaxStrips = 8;  // named barriers 1..8 (15 is the consumer-wide one)
 constexpr int kMaxSmem = 227 * 1024;
 constexpr int kPx = 4;  // output columns per thread
 
@@ -41,12 +54,17 @@ struct TileGeom {
     int n_strips;
     int bands;      // ceil(crop / R)
     int rows_cap;   // source rows per plane a stage can hold
-    int pitch;      // bytes per staged source row (multiple of 16)
+    int pitch0;     // minimum staged row pitch; a clip uses pitch0 + ((w - pitch0) & 15) so that pitch == w (mod 16)
+    int plane_stride;  // bytes between the staged planes of a tile
     int stage_bytes;
     int strip_bytes;   // staging bytes of one strip buffer
     int bulk_store;    // 1: cp.async.bulk stores are legal (alignment), 0: plain stores
     int total_tiles;
     int off_ytab, off_in, off_out, off_lut;
+    int stages;      // input ring depth (2 or 3)
+    int out_bufs;    // staging buffers per strip (2 = double-buffered, 1 = wait before rewriting)
+    int na_uniform;  // AFFINE: all channels share one scale, so it is folded into the row table
+    int debug;       // PVA_TILED_DEBUG bits (experiments only): 1 no stores, 2 no loads, 4 no compute
 };
 
 struct TiledArgs {
@@ -88,6 +106,7 @@ __device__ __forceinline__ void bulk_store(void* dst, uint32_t src, uint32_t byt
 }
 __device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void bulk_wait_read_all() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_read_but_one() { asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory"); }
 __device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
 __device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 __device__ __forceinline__ void named_bar(int id, int count) {
@@ -131,74 +150,75 @@ struct Pack<__nv_bfloat16> {
     }
 };
 
-// Write the thread's 4 px x 3 ch results of one output row into the staging strip.
-// THWC: 12 consecutive elements at element offset row*crop*3 + 12*g.
-// CTHW: 4 consecutive elements per channel at c*rows*crop + row*crop + 4*g.
-template <typename OutT, int kLayout>
-__device__ __forceinline__ void stage_row(unsigned char* strip, int row, int rows, int crop, int g, bool full,
+// Write the thread's 4 px x 3 ch results of one output row into the staging strip, in final
+// T x S x S x C order: 12 consecutive elements at element offset row * crop * 3 + 12 * g.
+template <typename OutT>
+__device__ __forceinline__ void stage_row(unsigned char* strip, int row, int crop, int g, bool full,
                                           const float (&o)[kPx][3]) {
-    if (kLayout == kLayoutTHWC) {
-        OutT* base = reinterpret_cast<OutT*>(strip) + (size_t)row * crop * 3 + 12 * g;
-        if (full) {
-            if (sizeof(OutT) == 4) {
-                float4* d = reinterpret_cast<float4*>(base);
-                d[0] = make_float4(o[0][0], o[0][1], o[0][2], o[1][0]);
-                d[1] = make_float4(o[1][1], o[1][2], o[2][0], o[2][1]);
-                d[2] = make_float4(o[2][2], o[3][0], o[3][1], o[3][2]);
-            } else {
-                using P = Pack<typename std::conditional<sizeof(OutT) == 2, OutT, __half>::type>;
-                uint2* d = reinterpret_cast<uint2*>(base);
-                d[0] = make_uint2(P::two(o[0][0], o[0][1]), P::two(o[0][2], o[1][0]));
-                d[1] = make_uint2(P::two(o[1][1], o[1][2]), P::two(o[2][0], o[2][1]));
-                d[2] = make_uint2(P::two(o[2][2], o[3][0]), P::two(o[3][1], o[3][2]));
-            }
+    OutT* base = reinterpret_cast<OutT*>(strip) + (size_t)row * crop * 3 + 12 * g;
+    if (full) {
+        if (sizeof(OutT) == 4) {
+            float4* d = reinterpret_cast<float4*>(base);
+            d[0] = make_float4(o[0][0], o[0][1], o[0][2], o[1][0]);
+            d[1] = make_float4(o[1][1], o[1][2], o[2][0], o[2][1]);
+            d[2] = make_float4(o[2][2], o[3][0], o[3][1], o[3][2]);
         } else {
-            const int npx = crop - kPx * g;
-#pragma unroll
-            for (int i = 0; i < kPx; ++i)
-                if (i < npx)
-#pragma unroll
-                    for (int c = 0; c < 3; ++c) base[i * 3 + c] = to_out<OutT>(o[i][c]);
+            using P = Pack<typename std::conditional<sizeof(OutT) == 2, OutT, __half>::type>;
+            uint2* d = reinterpret_cast<uint2*>(base);
+            d[0] = make_uint2(P::two(o[0][0], o[0][1]), P::two(o[0][2], o[1][0]));
+            d[1] = make_uint2(P::two(o[1][1], o[1][2]), P::two(o[2][0], o[2][1]));
+            d[2] = make_uint2(P::two(o[2][2], o[3][0]), P::two(o[3][1], o[3][2]));
         }
     } else {
+        const int npx = crop - kPx * g;
 #pragma unroll
-        for (int c = 0; c < 3; ++c) {
-            OutT* base = reinterpret_cast<OutT*>(strip) + ((size_t)c * rows + row) * crop + kPx * g;
-            if (full && (crop & 3) == 0) {
-                if (sizeof(OutT) == 4) {
-                    *reinterpret_cast<float4*>(base) = make_float4(o[0][c], o[1][c], o[2][c], o[3][c]);
-                } else {
-                    using P = Pack<typename std::conditional<sizeof(OutT) == 2, OutT, __half>::type>;
-                    *reinterpret_cast<uint2*>(base) = make_uint2(P::two(o[0][c], o[1][c]), P::two(o[2][c], o[3][c]));
-                }
-            } else {
-                const int npx = crop - kPx * g;
+        for (int i = 0; i < kPx; ++i)
+            if (i < npx)
 #pragma unroll
-                for (int i = 0; i < kPx; ++i)
-                    if (i < npx) base[i] = to_out<OutT>(o[i][c]);
-            }
-        }
+                for (int c = 0; c < 3; ++c) base[i * 3 + c] = to_out<OutT>(o[i][c]);
     }
 }
 
-template <typename OutT, int kLayout, int kNorm>
+__device__ __forceinline__ void cp_async16(uint32_t dst, const void* src) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
+}
+// arrive on the mbarrier once all cp.async issued so far by this thread have landed
+__device__ __forceinline__ void cp_async_arrive(uint32_t bar) {
+    asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(bar) : "memory");
+}
+
+// Two bytes of t (compile-time positions) as a half2 of fp16 SUBNORMALS: the 16-bit pattern
+// 0x00bb is exactly b * 2^-24, so zero-extension is the whole integer->float conversion and
+// cvt.f32.f16 finishes it.  The 2^24 is folded into the row weights.
+template <int lo, int hi>
+__device__ __forceinline__ __half2 bytes_as_half2(uint32_t t) {
+    const uint32_t v = __byte_perm(t, 0u, 0x4040u | lo | (hi << 8));
+    return *reinterpret_cast<const __half2*>(&v);
+}
+
+// kNormT: 0 = EXACT, 1 = AFFINE with one scale for all channels (folded into the row table),
+// 2 = AFFINE with per-channel scales.
+template <typename OutT, int kNormT, bool kFastX>
 __global__ void __launch_bounds__(kBlockThreads, 1) pva_tiled_kernel(const __grid_constant__ TiledArgs a) {
     extern __shared__ __align__(128) unsigned char smem[];
+    constexpr int kNorm = kNormT == 0 ? kNormExact : kNormAffine;
+    constexpr bool kUniformNa = kNormT == 1;
     const KParams& p = a.p;
     const TileGeom& tg = a.g;
-    __shared__ __align__(8) unsigned long long s_full[kStages];
-    __shared__ __align__(8) unsigned long long s_empty[kStages];
+    __shared__ __align__(8) unsigned long long s_full[kMaxStages];
+    __shared__ __align__(8) unsigned long long s_empty[kMaxStages];
 
     const int tid = threadIdx.x;
     const int crop = p.crop;
-    // contiguous tile range of this CTA
+    const int n_stages = tg.stages;
+    // contiguous tile range of this CTA (tiles are ordered clip, frame, band)
     const int t_begin = (int)(((long long)tg.total_tiles * blockIdx.x) / gridDim.x);
     const int t_end = (int)(((long long)tg.total_tiles * (blockIdx.x + 1)) / gridDim.x);
     const int tiles_per_clip = p.n_fast * tg.bands;
 
     if (tid == 0) {
-        for (int s = 0; s < kStages; ++s) {
-            mbar_init(smem_u32(&s_full[s]), 1);
+        for (int s = 0; s < kMaxStages; ++s) {
+            mbar_init(smem_u32(&s_full[s]), 1);  // the producer's arrive.expect_tx; the copies complete the tx count
             mbar_init(smem_u32(&s_empty[s]), kConsumerThreads / 32);
         }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -214,48 +234,46 @@ __global__ void __launch_bounds__(kBlockThreads, 1) pva_tiled_kernel(const __gri
     if (tid >= kConsumerThreads) {
         // ------------------------------ producer warp ------------------------------
         const int lane = tid - kConsumerThreads;
-        int cur_clip = -1, ca = 0, ncols = 0;
-        for (int t = t_begin, it = 0; t < t_end; ++t, ++it) {
+        int cur_clip = -1, ca = 0, ncols = 0, W = 0, H = 0, T_in = 0, pitch = 0, top = 0, idx_row = 0;
+        float sy = 0.f;
+        const uint8_t* src = nullptr;
+        int s = 0;
+        uint32_t ph = 0;
+        for (int t = t_begin; t < t_end; ++t) {
             const int clip_i = t / tiles_per_clip;
             const int rem = t - clip_i * tiles_per_clip;
             const int k = rem / tg.bands;
             const int band = rem - k * tg.bands;
-            const ClipGeom& g = p.clips[clip_i];
             if (clip_i != cur_clip) {
                 cur_clip = clip_i;
+                const ClipGeom& g = p.clips[clip_i];
+                src = g.src, W = g.w, H = g.h, T_in = g.t_in, sy = g.sy, top = g.top, idx_row = g.idx_row;
                 src_range(g.sx, g.left, g.left + crop - 1, g.w, ca, ncols);
+                pitch = W;
             }
             const int yb = band * tg.R;
             const int ye = min(yb + tg.R, crop);
             int ra, nrows;
-            src_range(g.sy, g.top + yb, g.top + ye - 1, g.h, ra, nrows);
-            const int s = it % kStages;
-            const uint32_t ph = (uint32_t)(it / kStages) & 1u;
+            src_range(sy, top + yb, top + ye - 1, H, ra, nrows);
             mbar_wait(smem_u32(&s_empty[s]), ph ^ 1u);
-            const int t_src = p.frame_idx[g.idx_row][k];
-            const size_t plane_sz = (size_t)g.h * g.w;
-            const int n_copies = 3 * nrows;
-            // bytes first (expect_tx must cover every copy of the phase), then the copies
-            uint32_t my_bytes = 0;
-            for (int j = lane; j < n_copies; j += 32) {
-                const int c = j / nrows, r = j - c * nrows;
-                const uintptr_t ga = (uintptr_t)(g.src + ((size_t)c * g.t_in + t_src) * plane_sz + (size_t)(ra + r) * g.w + ca);
-                const uintptr_t al = ga & ~(uintptr_t)15;
-                my_bytes += (uint32_t)(((ga + ncols - al) + 15) & ~(uintptr_t)15);
-            }
-#pragma unroll
-            for (int o = 16; o > 0; o >>= 1) my_bytes += __shfl_xor_sync(0xffffffffu, my_bytes, o);
-            const uint32_t bar = smem_u32(&s_full[s]);
-            if (lane == 0) mbar_arrive_expect_tx(bar, my_bytes);
-            __syncwarp();
+            const int t_src = p.frame_idx[idx_row][k];
             const uint32_t st_base = in_base + (uint32_t)s * tg.stage_bytes;
-            for (int j = lane; j < n_copies; j += 32) {
-                const int c = j / nrows, r = j - c * nrows;
-                const uintptr_t ga = (uintptr_t)(g.src + ((size_t)c * g.t_in + t_src) * plane_sz + (size_t)(ra + r) * g.w + ca);
-                const uintptr_t al = ga & ~(uintptr_t)15;
-                const uint32_t bytes = (uint32_t)(((ga + ncols - al) + 15) & ~(uintptr_t)15);
-                bulk_load(st_base + (uint32_t)((c * tg.rows_cap + r) * tg.pitch), reinterpret_cast<const void*>(al), bytes, bar);
-            }
+            const uint32_t bar = smem_u32(&s_full[s]);
+            // One bulk copy per plane: the whole band of source rows, first needed byte (ra, ca) to
+            // last needed byte, rounded out to 16-byte granules.  Rows are contiguous in memory, so
+            // this is a single linear range; staged byte (r, col) sits at
+            //   plane base + (g0 & 15) + (r - ra) * W + (col - ca).
+            const uint8_t* g0 = src + (((size_t)min(lane, 2) * T_in + t_src) * H + ra) * W + ca;
+            const uint32_t sh = (uint32_t)((uintptr_t)g0 & 15);
+            const uint32_t bytes = (sh + (uint32_t)(nrows - 1) * (uint32_t)W + (uint32_t)ncols + 15u) & ~15u;
+            uint32_t total = lane < 3 ? bytes : 0u;
+            total += __shfl_xor_sync(0xffffffffu, total, 1);
+            total += __shfl_xor_sync(0xffffffffu, total, 2);
+            if (tg.debug & 2) total = 0;
+            if (lane == 0) mbar_arrive_expect_tx(bar, total);
+            __syncwarp();
+            if (lane < 3 && !(tg.debug & 2)) bulk_load(st_base + (uint32_t)lane * tg.plane_stride, g0 - sh, bytes, bar);
+            if (++s == n_stages) s = 0, ph ^= 1u;
         }
         return;
     }
@@ -264,47 +282,54 @@ __global__ void __launch_bounds__(kBlockThreads, 1) pva_tiled_kernel(const __gri
     const int strip = tid / tg.tps;
     const int g_col = tid - strip * tg.tps;  // column group of this thread
     const int gx = (crop + kPx - 1) / kPx;
-    const bool active_col = g_col < gx && strip < tg.n_strips;
+    const bool in_strip = strip < tg.n_strips;
+    const bool active_col = g_col < gx && in_strip;
     const bool full_group = (kPx * g_col + kPx) <= crop && (crop & 3) == 0;  // vector staging stores need crop % 4 == 0
     const int strip_threads = tg.tps;
     int4* ytab = reinterpret_cast<int4*>(smem + tg.off_ytab);
-    unsigned char* out_base = smem + tg.off_out + (size_t)strip * 2 * tg.strip_bytes;
+    unsigned char* out_base = smem + tg.off_out + (size_t)strip * tg.out_bufs * tg.strip_bytes;
     const float* lut = reinterpret_cast<const float*>(smem + tg.off_lut);
     const size_t esz = sizeof(OutT);
 
-    // per-clip, per-thread column state
+    // per-clip state, cached in registers
     int cur_clip = -1;
-    int ca = 0;
-    bool fastx = false;
-    int woff = 0;             // fast path: byte offset (from column ca) of the thread's aligned 8-byte window
-    uint32_t sel0 = 0, sel1 = 0;
-    int off0[kPx], off1[kPx];  // byte path: offsets from column ca
+    int ca = 0, W = 0, H = 0, T_in = 0, pitch = 0, idx_row = 0;
+    const uint8_t* src = nullptr;
+    int woff = 0;               // kFastX: byte offset (from column ca) of the thread's aligned 8-byte window
+    uint32_t sel0 = 0, sel1 = 0;  // kFastX: PRMT selectors picking the 4 left / right taps out of the window
+    int off0[kPx], off1[kPx];   // !kFastX: byte offsets of the taps from column ca
     float lx0[kPx], lx1[kPx];
 #pragma unroll
     for (int i = 0; i < kPx; ++i) off0[i] = off1[i] = 0, lx0[i] = lx1[i] = 0.f;
 
-    int strip_it = 0;  // staging double-buffer index of this strip
+    int strip_it = 0;  // staging buffer index of this strip
+    int s = 0;
+    uint32_t ph = 0;
 
-    for (int t = t_begin, it = 0; t < t_end; ++t, ++it) {
+    for (int t = t_begin; t < t_end; ++t) {
         const int clip_i = t / tiles_per_clip;
         const int rem = t - clip_i * tiles_per_clip;
         const int k = rem / tg.bands;
         const int band = rem - k * tg.bands;
-        const ClipGeom& g = p.clips[clip_i];
 
         if (clip_i != cur_clip) {
             // every strip must have left the previous clip before the row table is rebuilt
             named_bar(15, kConsumerThreads);
             cur_clip = clip_i;
+            const ClipGeom& g = p.clips[clip_i];
+            src = g.src, W = g.w, H = g.h, T_in = g.t_in, idx_row = g.idx_row;
+            pitch = W;  // the staged band is a linear image of the source rows
+            // AFFINE: the row weights absorb the 2^24 of the subnormal trick and, when all
+            // channels share it, the normalisation scale 1 / (255 std)
+            const float wscale = (kNorm == kNormAffine) ? 16777216.0f * (kUniformNa ? p.na[0] : 1.0f) : 1.0f;
             for (int y = tid; y < crop; y += kConsumerThreads) {
                 int y0, y1;
                 float l0, l1;
                 bilinear_taps(g.sy, g.top + y, g.h, y0, y1, l0, l1);
-                ytab[y] = make_int4(y0, y1, __float_as_int(l0), __float_as_int(l1));
+                ytab[y] = make_int4(y0, y1, __float_as_int(l0 * wscale), __float_as_int(l1 * wscale));
             }
             int dummy;
             src_range(g.sx, g.left, g.left + crop - 1, g.w, ca, dummy);
-            fastx = (g.flip >> 8) != 0;  // host: sx <= 1, w % 4 == 0, src % 4 == 0
             int xmin = 0x7fffffff;
             int x0v[kPx], x1v[kPx];
 #pragma unroll
@@ -327,180 +352,185 @@ __global__ void __launch_bounds__(kBlockThreads, 1) pva_tiled_kernel(const __gri
             named_bar(15, kConsumerThreads);
         }
 
-        const int s = it % kStages;
-        const uint32_t ph = (uint32_t)(it / kStages) & 1u;
         const int yb = band * tg.R;
         const int ye = min(yb + tg.R, crop);
         const int y_begin = yb + strip * tg.rps;
         const int y_end = min(y_begin + tg.rps, ye);
         const int rows = max(y_end - y_begin, 0);
-        unsigned char* stage_out = out_base + (size_t)(strip_it & 1) * tg.strip_bytes;
+        unsigned char* stage_out = out_base + (size_t)strip_it * tg.strip_bytes;
+
+        if (tg.out_bufs == 1 && tg.bulk_store && in_strip) {
+            // single staging buffer: the previous tile's store must have drained it
+            if (g_col == 0) bulk_wait_read_all();
+            named_bar(1 + strip, strip_threads);
+        }
 
         mbar_wait(smem_u32(&s_full[s]), ph);
 
-        if (active_col && rows > 0) {
+        if (active_col && rows > 0 && !(tg.debug & 4)) {
             const int ra = ytab[yb].x;  // first source row staged for this tile
-            const int t_src = p.frame_idx[g.idx_row][k];
-            const uint32_t st_base = in_base + (uint32_t)s * tg.stage_bytes;
-            // low 4 address bits of (plane c, row 0, column ca); a row adds r * w
-            uint32_t k_c[3];
+            const int t_src = p.frame_idx[idx_row][k];
+            // staged address of (plane c, source row r, window start) = rowbase[c] + r * pitch
+            uint32_t rowbase[3];
 #pragma unroll
-            for (int c = 0; c < 3; ++c)
-                k_c[c] = (uint32_t)((uintptr_t)(g.src + ((size_t)c * g.t_in + t_src) * (size_t)g.h * g.w + ca));
+            for (int c = 0; c < 3; ++c) {
+                const uint32_t gc = (uint32_t)(uintptr_t)(src + (((size_t)c * T_in + t_src) * H + ra) * W + ca);
+                rowbase[c] = in_base + (uint32_t)s * tg.stage_bytes + (uint32_t)c * tg.plane_stride + (gc & 15u) +
+                             (uint32_t)(kFastX ? woff : 0) - (uint32_t)ra * (uint32_t)pitch;
+            }
 
-            // x-pass of one source row into h[i][c]
+            // x-pass of one source row into h[i][c].
+            //   EXACT : h = fma(lx0, lut[b0], lx1 * lut[b1])            (ATen's arithmetic)
+            //   AFFINE: h = fma(lx1, b1 - b0, b0) * 2^-24               (same value, one rounding)
             auto hrow = [&](int r, float (&h)[kPx][3]) {
+                const uint32_t ro = (uint32_t)r * (uint32_t)pitch;
 #pragma unroll
                 for (int c = 0; c < 3; ++c) {
-                    const uint32_t shift = (k_c[c] + (uint32_t)r * (uint32_t)g.w) & 15u;
-                    const uint32_t row_addr = st_base + (uint32_t)((c * tg.rows_cap + (r - ra)) * tg.pitch) + shift;
-                    uint32_t b0[kPx], b1[kPx];
-                    if (fastx) {
-                        const uint32_t w0 = lds32(row_addr + woff);
-                        const uint32_t w1 = lds32(row_addr + woff + 4);
+                    const uint32_t addr = rowbase[c] + ro;
+                    if (kFastX) {
+                        const uint32_t w0 = lds32(addr);
+                        const uint32_t w1 = lds32(addr + 4);
                         const uint32_t t0 = __byte_perm(w0, w1, sel0);
                         const uint32_t t1 = __byte_perm(w0, w1, sel1);
+                        if (kNorm == kNormExact) {
 #pragma unroll
-                        for (int i = 0; i < kPx; ++i) {
-                            b0[i] = (t0 >> (8 * i)) & 0xffu;
-                            b1[i] = (t1 >> (8 * i)) & 0xffu;
+                            for (int i = 0; i < kPx; ++i) {
+                                const float v0 = lut[c * 256 + ((t0 >> (8 * i)) & 0xffu)];
+                                const float v1 = lut[c * 256 + ((t1 >> (8 * i)) & 0xffu)];
+                                h[i][c] = fmaf(lx0[i], v0, lx1[i] * v1);
+                            }
+                        } else {
+                            const __half2 a01 = bytes_as_half2<0, 1>(t0), a23 = bytes_as_half2<2, 3>(t0);
+                            const __half2 b01 = bytes_as_half2<0, 1>(t1), b23 = bytes_as_half2<2, 3>(t1);
+                            const float2 v01 = __half22float2(a01), v23 = __half22float2(a23);
+                            const float2 d01 = __half22float2(__hsub2(b01, a01));  // exact: multiples of 2^-24
+                            const float2 d23 = __half22float2(__hsub2(b23, a23));
+                            h[0][c] = fmaf(lx1[0], d01.x, v01.x);
+                            h[1][c] = fmaf(lx1[1], d01.y, v01.y);
+                            h[2][c] = fmaf(lx1[2], d23.x, v23.x);
+                            h[3][c] = fmaf(lx1[3], d23.y, v23.y);
                         }
                     } else {
 #pragma unroll
                         for (int i = 0; i < kPx; ++i) {
-                            b0[i] = lds8(row_addr + off0[i]);
-                            b1[i] = lds8(row_addr + off1[i]);
+                            const uint32_t b0 = lds8(addr + off0[i]);
+                            const uint32_t b1 = lds8(addr + off1[i]);
+                            if (kNorm == kNormExact) {
+                                h[i][c] = fmaf(lx0[i], lut[c * 256 + b0], lx1[i] * lut[c * 256 + b1]);
+                            } else {
+                                const float v0 = (float)b0 * 5.9604644775390625e-08f;  // 2^-24, as on the fast path
+                                const float dd = (float)((int)b1 - (int)b0) * 5.9604644775390625e-08f;
+                                h[i][c] = fmaf(lx1[i], dd, v0);
+                            }
                         }
-                    }
-#pragma unroll
-                    for (int i = 0; i < kPx; ++i) {
-                        float v0, v1;
-                        if (kNorm == kNormExact) {
-                            v0 = lut[c * 256 + b0[i]];
-                            v1 = lut[c * 256 + b1[i]];
-                        } else {
-                            v0 = (float)b0[i];
-                            v1 = (float)b1[i];
-                        }
-                        h[i][c] = fmaf(lx0[i], v0, lx1[i] * v1);
                     }
                 }
             };
             // y-pass + normalisation epilogue + staging of one output row
-            auto emit = [&](int y, const int4& e, const float (&top)[kPx][3], const float (&bot)[kPx][3]) {
+            auto emit = [&](int y, const int4& e, const float (&tp)[kPx][3], const float (&bt)[kPx][3]) {
                 const float ly0 = __int_as_float(e.z), ly1 = __int_as_float(e.w);
                 float o[kPx][3];
+                if (kNorm == kNormExact) {
 #pragma unroll
-                for (int i = 0; i < kPx; ++i)
+                    for (int i = 0; i < kPx; ++i)
+#pragma unroll
+                        for (int c = 0; c < 3; ++c) o[i][c] = fmaf(ly0, tp[i][c], ly1 * bt[i][c]);
+                } else {
+                    // out = (ly0 top + ly1 bot) * na + nb, na folded into the row weights
 #pragma unroll
                     for (int c = 0; c < 3; ++c) {
-                        const float v = fmaf(ly0, top[i][c], ly1 * bot[i][c]);
-                        o[i][c] = (kNorm == kNormExact) ? v : fmaf(v, p.na[c], p.nb[c]);
+                        float w0 = ly0, w1 = ly1;
+                        if (!kUniformNa) w0 *= p.na[c], w1 *= p.na[c];
+                        const float b = p.nb[c];
+#pragma unroll
+                        for (int i = 0; i < kPx; ++i) o[i][c] = fmaf(w0, tp[i][c], fmaf(w1, bt[i][c], b));
                     }
-                stage_row<OutT, kLayout>(stage_out, y - y_begin, rows, crop, g_col, full_group, o);
+                }
+                stage_row<OutT>(stage_out, y - y_begin, crop, g_col, full_group, o);
+            };
+            // One output row.  T holds source row rT (the row's upper tap), B holds rB.  When the
+            // upper tap moves on to the row B already holds, the buffers swap roles (returns true)
+            // instead of being copied.
+            auto row_step = [&](int y, const int4& e, float (&T)[kPx][3], float (&B)[kPx][3], int& rT, int& rB) -> bool {
+                if (e.x == rB && e.x != rT) {
+                    if (e.y != rT) {
+                        hrow(e.y, T);
+                        rT = e.y;
+                    }
+                    emit(y, e, B, T);
+                    return true;
+                }
+                if (e.x != rT) {
+                    hrow(e.x, T);
+                    rT = e.x;
+                }
+                if (e.y != rB) {
+                    hrow(e.y, B);
+                    rB = e.y;
+                }
+                emit(y, e, T, B);
+                return false;
             };
 
             float hA[kPx][3], hB[kPx][3];
-            int y = y_begin;
-            int4 e = ytab[y];
-            int r = e.x;
-            hrow(r, hA);
-            // Source-row-driven walk; X holds source row r.  Returns true when the strip is done,
-            // false after moving on to row r + 1 (held in Y): the caller swaps the roles.
-            auto step = [&](float (&X)[kPx][3], float (&Y)[kPx][3]) -> bool {
-                while (true) {
-                    while (y < y_end && e.y == r) {  // both taps on row r (clamped at the bottom edge)
-                        emit(y, e, X, X);
-                        if (++y < y_end) e = ytab[y];
-                    }
-                    if (y >= y_end) return true;
-                    if (e.x != r) {  // down-scaling skipped a source row
-                        r = e.x;
-                        hrow(r, X);
-                        continue;
-                    }
-                    hrow(r + 1, Y);
-                    while (y < y_end && e.x == r) {  // taps on rows r, r + 1
-                        emit(y, e, X, Y);
-                        if (++y < y_end) e = ytab[y];
-                    }
-                    r = r + 1;
-                    return y >= y_end;
+            int rA = -1, rB = -1;
+            bool top_is_a = true;
+#pragma unroll 1
+            for (int y = y_begin; y < y_end; ++y) {
+                const int4 e = ytab[y];
+                if (top_is_a) {
+                    if (row_step(y, e, hA, hB, rA, rB)) top_is_a = false;
+                } else {
+                    if (row_step(y, e, hB, hA, rB, rA)) top_is_a = true;
                 }
-            };
-            while (true) {
-                if (step(hA, hB)) break;
-                if (step(hB, hA)) break;
             }
         }
 
         // this warp no longer reads the input stage
         __syncwarp();
         if ((tid & 31) == 0) mbar_arrive(smem_u32(&s_empty[s]));
+        if (++s == n_stages) s = 0, ph ^= 1u;
 
-        if (strip < tg.n_strips) {
+        if (in_strip) {
             // ---- strip store: staging -> global (fast pathway, and slow when frame k belongs to it)
             OutT* fast = reinterpret_cast<OutT*>(p.fast_out) + (size_t)clip_i * p.fast_clip_elems;
             OutT* slow = p.slow_out ? reinterpret_cast<OutT*>(p.slow_out) + (size_t)clip_i * p.slow_clip_elems : nullptr;
             if (tg.bulk_store) {
                 fence_async_smem();  // generic-proxy writes of the strip -> visible to the async proxy
-                if (g_col == 0) bulk_wait_read_all();  // the other staging buffer's previous store has drained
+                // double-buffered: the other buffer's store (issued a tile ago) must have drained
+                // before anyone runs ahead into the next tile and overwrites it
+                if (g_col == 0) {
+                    if (tg.out_bufs == 2) bulk_wait_read_all();
+                    if (tg.out_bufs == 3) bulk_wait_read_but_one();  // the store before last has drained
+                }
                 named_bar(1 + strip, strip_threads);
-                if (g_col == 0 && rows > 0) {
-                    const uint32_t src = smem_u32(stage_out);
-                    if (kLayout == kLayoutTHWC) {
-                        const uint32_t bytes = (uint32_t)((size_t)rows * crop * 3 * esz);
-                        bulk_store(fast + ((size_t)k * crop + y_begin) * crop * 3, src, bytes);
-                        if (slow)
-                            for (int j = 0; j < p.n_slow; ++j)
-                                if (p.slow_idx[j] == k)
-                                    bulk_store(slow + ((size_t)j * crop + y_begin) * crop * 3, src, bytes);
-                    } else {
-                        const uint32_t bytes = (uint32_t)((size_t)rows * crop * esz);
-#pragma unroll
-                        for (int c = 0; c < 3; ++c) {
-                            bulk_store(fast + (((size_t)c * p.n_fast + k) * crop + y_begin) * crop, src + c * bytes, bytes);
-                            if (slow)
-                                for (int j = 0; j < p.n_slow; ++j)
-                                    if (p.slow_idx[j] == k)
-                                        bulk_store(slow + (((size_t)c * p.n_slow + j) * crop + y_begin) * crop,
-                                                   src + c * bytes, bytes);
-                        }
-                    }
+                if (g_col == 0 && rows > 0 && !(tg.debug & 1)) {
+                    const uint32_t ssrc = smem_u32(stage_out);
+                    const uint32_t bytes = (uint32_t)((size_t)rows * crop * 3 * esz);
+                    bulk_store(fast + ((size_t)k * crop + y_begin) * crop * 3, ssrc, bytes);
+                    if (slow)
+                        for (int j = 0; j < p.n_slow; ++j)
+                            if (p.slow_idx[j] == k) bulk_store(slow + ((size_t)j * crop + y_begin) * crop * 3, ssrc, bytes);
                     bulk_commit();
                 }
-                ++strip_it;
+                if (++strip_it >= tg.out_bufs) strip_it = 0;
             } else {
                 // alignment does not allow bulk stores: cooperative element copy by the strip
                 named_bar(1 + strip, strip_threads);
                 const OutT* st = reinterpret_cast<const OutT*>(stage_out);
-                const int per_c = rows * crop;
-                const int n_el = per_c * 3;
+                const int n_el = rows * crop * 3;
                 for (int idx = g_col; idx < n_el; idx += strip_threads) {
-                    size_t off_f, off_s_base;
-                    if (kLayout == kLayoutTHWC) {
-                        off_f = ((size_t)k * crop + y_begin) * crop * 3 + idx;
-                        off_s_base = (size_t)y_begin * crop * 3 + idx;
-                    } else {
-                        const int c = idx / per_c, w = idx - c * per_c;
-                        off_f = (((size_t)c * p.n_fast + k) * crop + y_begin) * crop + w;
-                        off_s_base = ((size_t)c * p.n_slow * crop + y_begin) * crop + w;
-                    }
                     const OutT v = st[idx];
-                    fast[off_f] = v;
+                    fast[((size_t)k * crop + y_begin) * crop * 3 + idx] = v;
                     if (slow)
                         for (int j = 0; j < p.n_slow; ++j)
-                            if (p.slow_idx[j] == k) {
-                                const size_t fr = (kLayout == kLayoutTHWC) ? (size_t)j * crop * crop * 3
-                                                                           : (size_t)j * crop * crop;
-                                slow[off_s_base + fr] = v;
-                            }
+                            if (p.slow_idx[j] == k) slow[((size_t)j * crop + y_begin) * crop * 3 + idx] = v;
                 }
                 named_bar(1 + strip, strip_threads);  // staging may be overwritten by the next tile
             }
         }
     }
-    if (tg.bulk_store && g_col == 0 && strip < tg.n_strips) bulk_wait_all();
+    if (tg.bulk_store && g_col == 0 && in_strip) bulk_wait_all();
 }
 
 int round_up(int v, int m) { return (v + m - 1) / m * m; }
@@ -516,9 +546,17 @@ void host_taps(float scale, int dst, int in_size, int* i0, int* i1) {
     *i1 = b;
 }
 
-// Choose rows-per-strip and the shared-memory carve-up; false if nothing fits.
+int env_int(const char* name, int dflt) {
+    const char* v = getenv(name);
+    return v ? atoi(v) : dflt;
+}
+
+// Choose rows-per-strip, ring depth and the shared-memory carve-up; false if nothing fits.
 bool plan_tiles(const KParams& p, int out_dtype, int layout, TileGeom* tg, const char** why) {
-    (void)layout;
+    if (layout != kLayoutTHWC) {
+        *why = "tiled kernel writes the channels-last (T x S x S x C) layout only";
+        return false;
+    }
     if (p.C != 3) {
         *why = "tiled kernel handles 3-channel clips";
         return false;
@@ -527,10 +565,11 @@ bool plan_tiles(const KParams& p, int out_dtype, int layout, TileGeom* tg, const
     const int gx = (crop + kPx - 1) / kPx;
     const int tps = round_up(gx, 32);
     if (tps > kConsumerThreads) {
-        *why = "crop wider than 1024";
+        *why = "crop wider than 2048";
         return false;
     }
-    const int n_strips = kConsumerThreads / tps;
+    int n_strips = kConsumerThreads / tps;
+    if (n_strips > kMaxStrips) n_strips = kMaxStrips;
     const int esz = out_dtype == 0 ? 4 : 2;
     const int row_bytes = crop * 3 * esz;
 
@@ -542,16 +581,30 @@ bool plan_tiles(const KParams& p, int out_dtype, int layout, TileGeom* tg, const
         host_taps(g.sx, g.left + crop - 1, g.w, &b0, &b1);
         max_cols = max_cols > (b1 - a0 + 1) ? max_cols : (b1 - a0 + 1);
     }
-    const int pitch = round_up(max_cols + 15 + 8, 16);  // + row shift + the 8-byte tap window overhang
+    const int pitch0 = 0;  // unused: staged rows keep the source pitch
     const int ytab_bytes = round_up(crop * 16, 128);
     const int lut_bytes = 3 * 256 * 4;
+    const bool bulk_ok = (row_bytes % 16) == 0 && ((uintptr_t)p.fast_out % 16 == 0) &&
+                         (!p.slow_out || (uintptr_t)p.slow_out % 16 == 0);
 
-    for (int rps = 8; rps >= 1; rps >>= 1) {
+    // candidate configurations in order of preference: (rows per strip, stages, staging buffers)
+    static const int kCand[][3] = {{8, 2, 1}, {4, 2, 3}, {4, 3, 2}, {4, 2, 2}, {4, 2, 1}, {2, 3, 2}, {2, 2, 2}, {2, 2, 1}, {1, 2, 2}, {1, 2, 1}};
+    const int force_rps = env_int("PVA_TILED_RPS", 0), force_bufs = env_int("PVA_TILED_OUTBUFS", 0),
+              force_stages = env_int("PVA_TILED_STAGES", 0);
+    for (const auto& cand : kCand) {
+        const int rps = cand[0], stages = cand[1], out_bufs = bulk_ok ? cand[2] : 1;
+        if (force_rps && rps != force_rps) continue;
+        if (force_bufs && cand[2] != force_bufs) continue;
+        if (force_stages && stages != force_stages) continue;
         const int R = rps * n_strips;
         const int bands = (crop + R - 1) / R;
-        int rows_cap = 0;
+        int rows_cap = 0, band_bytes = 0;
         for (int i = 0; i < p.n_clips; ++i) {
             const ClipGeom& g = p.clips[i];
+            int c0, c1, d0, d1;
+            host_taps(g.sx, g.left, g.w, &c0, &c1);
+            host_taps(g.sx, g.left + crop - 1, g.w, &d0, &d1);
+            const int ncols = d1 - c0 + 1;
             for (int b = 0; b < bands; ++b) {
                 const int yb = b * R, ye = (yb + R < crop ? yb + R : crop);
                 int a0, a1, b0, b1;
@@ -559,9 +612,13 @@ bool plan_tiles(const KParams& p, int out_dtype, int layout, TileGeom* tg, const
                 host_taps(g.sy, g.top + ye - 1, g.h, &b0, &b1);
                 const int n = b1 - a0 + 1;
                 rows_cap = rows_cap > n ? rows_cap : n;
+                const int bytes = (n - 1) * g.w + ncols;
+                band_bytes = band_bytes > bytes ? band_bytes : bytes;
             }
         }
-        const int stage_bytes = round_up(3 * rows_cap * pitch, 128);
+        // + 15 leading alignment bytes, rounded to a granule, + the 8-byte tap window overhang
+        const int plane_stride = round_up(band_bytes + 15 + 16 + 8, 16);
+        const int stage_bytes = round_up(3 * plane_stride, 128);
         const int strip_bytes = round_up(rps * row_bytes, 128);
         int off = 0;
         tg->off_ytab = off;
@@ -570,9 +627,9 @@ bool plan_tiles(const KParams& p, int out_dtype, int layout, TileGeom* tg, const
         off += lut_bytes;
         off = round_up(off, 128);
         tg->off_in = off;
-        off += kStages * stage_bytes;
+        off += stages * stage_bytes;
         tg->off_out = off;
-        off += n_strips * 2 * strip_bytes;
+        off += n_strips * out_bufs * strip_bytes;
         if (off + 1024 > kMaxSmem) continue;
         tg->R = R;
         tg->rps = rps;
@@ -580,17 +637,18 @@ bool plan_tiles(const KParams& p, int out_dtype, int layout, TileGeom* tg, const
         tg->n_strips = n_strips;
         tg->bands = bands;
         tg->rows_cap = rows_cap;
-        tg->pitch = pitch;
+        tg->pitch0 = pitch0;
+        tg->plane_stride = plane_stride;
         tg->stage_bytes = stage_bytes;
         tg->strip_bytes = strip_bytes;
-        // bulk stores need 16-byte aligned global addresses and sizes for every strip
-        const bool thwc = layout == kLayoutTHWC;
-        // every strip offset and size is a multiple of `unit` (bytes of one output row, per channel for CTHW)
-        const long long unit = thwc ? (long long)row_bytes : (long long)crop * esz;
-        bool ok = (unit % 16) == 0;
-        ok = ok && ((uintptr_t)p.fast_out % 16 == 0) && (!p.slow_out || (uintptr_t)p.slow_out % 16 == 0);
-        tg->bulk_store = ok ? 1 : 0;
+        tg->stages = stages;
+        tg->out_bufs = out_bufs;
+        // bulk stores need 16-byte aligned global addresses and sizes: every strip offset and
+        // size is a multiple of the bytes of one output row
+        tg->bulk_store = bulk_ok ? 1 : 0;
         tg->total_tiles = p.n_clips * p.n_fast * bands;
+        tg->na_uniform = (p.na[0] == p.na[1] && p.na[1] == p.na[2]) ? 1 : 0;
+        tg->debug = env_int("PVA_TILED_DEBUG", 0);
         return true;
     }
     *why = "tile does not fit shared memory (source rows too wide for this scale)";
@@ -598,19 +656,21 @@ bool plan_tiles(const KParams& p, int out_dtype, int layout, TileGeom* tg, const
 }
 
 template <typename OutT>
-cudaError_t launch_t(const TiledArgs& a, int layout, int norm, int grid, int smem, cudaStream_t stream) {
-#define PVA_TILED_CASE(L, N)                                                                              \
-    if (layout == L && norm == N) {                                                                       \
-        auto kern = pva_tiled_kernel<OutT, L, N>;                                                         \
-        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);     \
-        if (e != cudaSuccess) return e;                                                                   \
-        kern<<<grid, kBlockThreads, smem, stream>>>(a);                                                   \
-        return cudaGetLastError();                                                                        \
+cudaError_t launch_t(const TiledArgs& a, int norm, bool fastx, int grid, int smem, cudaStream_t stream) {
+#define PVA_TILED_CASE(N, F)                                                                          \
+    if (norm == N && fastx == F) {                                                                    \
+        auto kern = pva_tiled_kernel<OutT, N, F>;                                                     \
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem); \
+        if (e != cudaSuccess) return e;                                                               \
+        kern<<<grid, kBlockThreads, smem, stream>>>(a);                                               \
+        return cudaGetLastError();                                                                    \
     }
-    PVA_TILED_CASE(kLayoutCTHW, kNormExact)
-    PVA_TILED_CASE(kLayoutCTHW, kNormAffine)
-    PVA_TILED_CASE(kLayoutTHWC, kNormExact)
-    PVA_TILED_CASE(kLayoutTHWC, kNormAffine)
+    PVA_TILED_CASE(0, false)
+    PVA_TILED_CASE(0, true)
+    PVA_TILED_CASE(1, false)
+    PVA_TILED_CASE(1, true)
+    PVA_TILED_CASE(2, false)
+    PVA_TILED_CASE(2, true)
 #undef PVA_TILED_CASE
     return cudaErrorInvalidValue;
 }
@@ -626,27 +686,29 @@ cudaError_t launch_tiled(KParams& p, int out_dtype, int layout, int norm, cudaSt
     static thread_local TiledArgs a;  // 13 KB: keep it off the stack
     const char* why = "";
     if (!plan_tiles(p, out_dtype, layout, &a.g, &why)) return cudaErrorInvalidConfiguration;
-    // per-clip fast x-path flag (bit 8 of flip): up-scaling or identity in x, 4-byte aligned rows
+    // the fast x-path needs, for every clip of the launch: up-scaling or identity in x (so that
+    // the taps of 4 adjacent outputs fit an aligned 8-byte window) and 4-byte aligned rows
+    bool fastx = true;
     for (int i = 0; i < p.n_clips; ++i) {
-        ClipGeom& g = p.clips[i];
-        const bool fastx = (g.w <= g.ow) && (g.w % 4 == 0) && ((uintptr_t)g.src % 4 == 0);
-        g.flip = (uint16_t)((g.flip & 1) | (fastx ? 0x100 : 0));
+        const ClipGeom& g = p.clips[i];
+        fastx = fastx && (g.w <= g.ow) && (g.w % 4 == 0) && ((uintptr_t)g.src % 4 == 0);
     }
     a.p = p;
     int dev = 0, sms = 148;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     int grid = sms < a.g.total_tiles ? sms : a.g.total_tiles;
-    const int smem = a.g.off_out + a.g.n_strips * 2 * a.g.strip_bytes;
+    const int smem = a.g.off_out + a.g.n_strips * a.g.out_bufs * a.g.strip_bytes;
+    const int kind = norm == kNormExact ? 0 : (a.g.na_uniform ? 1 : 2);
     cfg->rows_per_tile = a.g.R;
     cfg->smem_bytes = smem;
     cfg->grid = grid;
     cfg->block = kBlockThreads;
     cfg->tiles = a.g.total_tiles;
     switch (out_dtype) {
-        case 0: return launch_t<float>(a, layout, norm, grid, smem, stream);
-        case 1: return launch_t<__half>(a, layout, norm, grid, smem, stream);
-        case 2: return launch_t<__nv_bfloat16>(a, layout, norm, grid, smem, stream);
+        case 0: return launch_t<float>(a, kind, fastx, grid, smem, stream);
+        case 1: return launch_t<__half>(a, kind, fastx, grid, smem, stream);
+        case 2: return launch_t<__nv_bfloat16>(a, kind, fastx, grid, smem, stream);
         default: return cudaErrorInvalidValue;
     }
 }
