@@ -239,7 +239,9 @@ def run_b200_arm(args):
 
         dist.init_process_group("nccl", device_id=dev)
 
-    wl = WORKLOADS[args.workload]
+    wl = dict(WORKLOADS[args.workload])
+    if args.batch:
+        wl["batch"] = args.batch  # experiments only; the named workloads define the reported metric
     B, shape, kw = wl["batch"], wl["shape"], wl["kwargs"]
     t = pva_b200.make_transform(**kw, device=dev, out_dtype=torch.float16, channels_last=True,
                                 norm_mode=args.norm_mode, kernel=args.kernel)
@@ -426,7 +428,10 @@ def main():
     ap.add_argument("--e2e-steps", dest="e2e_steps", type=int, default=40)
     ap.add_argument("--cpu-seconds", dest="cpu_seconds", type=float, default=12.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--graph", action="store_true", help="replay the steps from a captured CUDA graph")
+    ap.add_argument("--batch", type=int, default=0, help="override the workload's batch (experiments)")
+    ap.add_argument("--graph", dest="graph", action="store_true", default=True,
+                    help="replay the steps from a captured CUDA graph (default)")
+    ap.add_argument("--no-graph", dest="graph", action="store_false", help="plain launches through the C ABI")
     args = ap.parse_args()
     if args.warmup < 3:
         args.warmup = 3  # timing rule: at least 3 warm-up steps

@@ -61,15 +61,24 @@ struct TileGeom {
     int bulk_store;    // 1: cp.async.bulk stores are legal (alignment), 0: plain stores
     int total_tiles;
     int off_ytab, off_in, off_out, off_lut;
+    int pdl;         // launched with programmatic stream serialization
+    int l2hint;      // bit 0: loads evict_first, bit 1: stores evict_first
     int stages;      // input ring depth (2 or 3)
     int out_bufs;    // staging buffers per strip (2 = double-buffered, 1 = wait before rewriting)
     int na_uniform;  // AFFINE: all channels share one scale, so it is folded into the row table
-    int debug;       // PVA_TILED_DEBUG bits (experiments only): 1 no stores, 2 no loads, 4 no compute
+    int debug;       // PVA_TILED_DEBUG bits (experiments only): 1 no stores, 2 no loads, 4 no compute,
+                     // 16 no proxy fence (wrong results)
 };
+
+constexpr int kMaxGrid = 160;
 
 struct TiledArgs {
     KParams p;
     TileGeom g;
+    // first tile of every CTA; tile_begin[grid] == total_tiles.  Equal tile counts by default: the
+    // kernel is bound by its writes, which are the same for every tile.  (A compute-cost-weighted
+    // split, PVA_TILED_BALANCE=1, measured 2 us slower.)
+    int tile_begin[kMaxGrid + 1];
 };
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -102,6 +111,22 @@ __device__ __forceinline__ void bulk_load(uint32_t dst, const void* src, uint32_
 }
 __device__ __forceinline__ void bulk_store(void* dst, uint32_t src, uint32_t bytes) {
     asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst), "r"(src), "r"(bytes)
+                 : "memory");
+}
+__device__ __forceinline__ uint64_t l2_evict_first_policy() {
+    uint64_t pol;
+    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+    return pol;
+}
+__device__ __forceinline__ void bulk_load_hint(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar, uint64_t pol) {
+    asm volatile(
+        "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;" ::"r"(dst),
+        "l"(src), "r"(bytes), "r"(bar), "l"(pol)
+        : "memory");
+}
+__device__ __forceinline__ void bulk_store_hint(void* dst, uint32_t src, uint32_t bytes, uint64_t pol) {
+    asm volatile("cp.async.bulk.global.shared::cta.bulk_group.L2::cache_hint [%0], [%1], %2, %3;" ::"l"(dst), "r"(src),
+                 "r"(bytes), "l"(pol)
                  : "memory");
 }
 __device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
@@ -212,8 +237,8 @@ __global__ void __launch_bounds__(kBlockThreads, 1) pva_tiled_kernel(const __gri
     const int crop = p.crop;
     const int n_stages = tg.stages;
     // contiguous tile range of this CTA (tiles are ordered clip, frame, band)
-    const int t_begin = (int)(((long long)tg.total_tiles * blockIdx.x) / gridDim.x);
-    const int t_end = (int)(((long long)tg.total_tiles * (blockIdx.x + 1)) / gridDim.x);
+    const int t_begin = a.tile_begin[blockIdx.x];
+    const int t_end = a.tile_begin[blockIdx.x + 1];
     const int tiles_per_clip = p.n_fast * tg.bands;
 
     if (tid == 0) {
@@ -228,12 +253,19 @@ __global__ void __launch_bounds__(kBlockThreads, 1) pva_tiled_kernel(const __gri
         for (int i = tid; i < 3 * 256; i += blockDim.x) lut[i] = p.lut[i];
     }
     __syncthreads();
+    if (tg.pdl) {
+        // Programmatic dependent launch: everything above ran while the previous kernel of the
+        // stream was still finishing; from here on global memory is touched, so wait for it.
+        asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+        asm volatile("griddepcontrol.wait;" ::: "memory");
+    }
 
     const uint32_t in_base = smem_u32(smem + tg.off_in);
 
     if (tid >= kConsumerThreads) {
         // ------------------------------ producer warp ------------------------------
         const int lane = tid - kConsumerThreads;
+        const uint64_t pol = l2_evict_first_policy();
         int cur_clip = -1, ca = 0, ncols = 0, W = 0, H = 0, T_in = 0, pitch = 0, top = 0, idx_row = 0;
         float sy = 0.f;
         const uint8_t* src = nullptr;
@@ -272,7 +304,10 @@ __global__ void __launch_bounds__(kBlockThreads, 1) pva_tiled_kernel(const __gri
             if (tg.debug & 2) total = 0;
             if (lane == 0) mbar_arrive_expect_tx(bar, total);
             __syncwarp();
-            if (lane < 3 && !(tg.debug & 2)) bulk_load(st_base + (uint32_t)lane * tg.plane_stride, g0 - sh, bytes, bar);
+            if (lane < 3 && !(tg.debug & 2)) {
+                if (tg.l2hint & 1) bulk_load_hint(st_base + (uint32_t)lane * tg.plane_stride, g0 - sh, bytes, bar, pol);
+                else bulk_load(st_base + (uint32_t)lane * tg.plane_stride, g0 - sh, bytes, bar);
+            }
             if (++s == n_stages) s = 0, ph ^= 1u;
         }
         return;
@@ -365,6 +400,7 @@ __global__ void __launch_bounds__(kBlockThreads, 1) pva_tiled_kernel(const __gri
             named_bar(1 + strip, strip_threads);
         }
 
+        // every thread polls: measured faster than one poller per warp + __syncwarp (43.4 vs 46.0 us)
         mbar_wait(smem_u32(&s_full[s]), ph);
 
         if (active_col && rows > 0 && !(tg.debug & 4)) {
@@ -496,7 +532,7 @@ __global__ void __launch_bounds__(kBlockThreads, 1) pva_tiled_kernel(const __gri
             OutT* fast = reinterpret_cast<OutT*>(p.fast_out) + (size_t)clip_i * p.fast_clip_elems;
             OutT* slow = p.slow_out ? reinterpret_cast<OutT*>(p.slow_out) + (size_t)clip_i * p.slow_clip_elems : nullptr;
             if (tg.bulk_store) {
-                fence_async_smem();  // generic-proxy writes of the strip -> visible to the async proxy
+                if (!(tg.debug & 16)) fence_async_smem();  // generic-proxy writes of the strip -> visible to the async proxy
                 // double-buffered: the other buffer's store (issued a tile ago) must have drained
                 // before anyone runs ahead into the next tile and overwrites it
                 if (g_col == 0) {
@@ -507,10 +543,19 @@ __global__ void __launch_bounds__(kBlockThreads, 1) pva_tiled_kernel(const __gri
                 if (g_col == 0 && rows > 0 && !(tg.debug & 1)) {
                     const uint32_t ssrc = smem_u32(stage_out);
                     const uint32_t bytes = (uint32_t)((size_t)rows * crop * 3 * esz);
-                    bulk_store(fast + ((size_t)k * crop + y_begin) * crop * 3, ssrc, bytes);
-                    if (slow)
-                        for (int j = 0; j < p.n_slow; ++j)
-                            if (p.slow_idx[j] == k) bulk_store(slow + ((size_t)j * crop + y_begin) * crop * 3, ssrc, bytes);
+                    if (tg.l2hint & 2) {
+                        const uint64_t pol = l2_evict_first_policy();
+                        bulk_store_hint(fast + ((size_t)k * crop + y_begin) * crop * 3, ssrc, bytes, pol);
+                        if (slow)
+                            for (int j = 0; j < p.n_slow; ++j)
+                                if (p.slow_idx[j] == k)
+                                    bulk_store_hint(slow + ((size_t)j * crop + y_begin) * crop * 3, ssrc, bytes, pol);
+                    } else {
+                        bulk_store(fast + ((size_t)k * crop + y_begin) * crop * 3, ssrc, bytes);
+                        if (slow)
+                            for (int j = 0; j < p.n_slow; ++j)
+                                if (p.slow_idx[j] == k) bulk_store(slow + ((size_t)j * crop + y_begin) * crop * 3, ssrc, bytes);
+                    }
                     bulk_commit();
                 }
                 if (++strip_it >= tg.out_bufs) strip_it = 0;
@@ -662,8 +707,17 @@ cudaError_t launch_t(const TiledArgs& a, int norm, bool fastx, int grid, int sme
         auto kern = pva_tiled_kernel<OutT, N, F>;                                                     \
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem); \
         if (e != cudaSuccess) return e;                                                               \
-        kern<<<grid, kBlockThreads, smem, stream>>>(a);                                               \
-        return cudaGetLastError();                                                                    \
+        cudaLaunchConfig_t cfg = {};                                                                  \
+        cfg.gridDim = dim3(grid);                                                                     \
+        cfg.blockDim = dim3(kBlockThreads);                                                           \
+        cfg.dynamicSmemBytes = smem;                                                                  \
+        cfg.stream = stream;                                                                          \
+        cudaLaunchAttribute attr[1];                                                                  \
+        attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;                              \
+        attr[0].val.programmaticStreamSerializationAllowed = 1;                                       \
+        cfg.attrs = attr;                                                                             \
+        cfg.numAttrs = a.g.pdl ? 1 : 0;                                                               \
+        return cudaLaunchKernelEx(&cfg, kern, a);                                                     \
     }
     PVA_TILED_CASE(0, false)
     PVA_TILED_CASE(0, true)
@@ -694,10 +748,36 @@ cudaError_t launch_tiled(KParams& p, int out_dtype, int layout, int norm, cudaSt
         fastx = fastx && (g.w <= g.ow) && (g.w % 4 == 0) && ((uintptr_t)g.src % 4 == 0);
     }
     a.p = p;
+    a.g.pdl = env_int("PVA_TILED_PDL", 1);
+    a.g.l2hint = env_int("PVA_TILED_L2HINT", 3);  // clip bytes are read once, outputs are consumed later: stream both
     int dev = 0, sms = 148;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     int grid = sms < a.g.total_tiles ? sms : a.g.total_tiles;
+    if (grid > kMaxGrid) grid = kMaxGrid;
+    {
+        // cost model per tile: emit + control per output row, x-pass per source row of a strip
+        const int tiles_per_clip = p.n_fast * a.g.bands;
+        double total = 0.0;
+        static thread_local double w[kMaxClipsPerLaunch];
+        for (int i = 0; i < p.n_clips; ++i) {
+            const double src_rows_per_strip = a.g.rps * (double)p.clips[i].sy + 1.5;
+            w[i] = env_int("PVA_TILED_BALANCE", 0) ? 62.0 * a.g.rps + 70.0 * src_rows_per_strip : 1.0;
+            total += w[i] * tiles_per_clip;
+        }
+        int clip = 0, t = 0;
+        double acc = 0.0;
+        a.tile_begin[0] = 0;
+        for (int b = 1; b < grid; ++b) {
+            const double target = total * b / grid;
+            while (t < a.g.total_tiles && acc + 0.5 * w[clip] <= target) {
+                acc += w[clip];
+                if (++t % tiles_per_clip == 0) ++clip;
+            }
+            a.tile_begin[b] = t;
+        }
+        a.tile_begin[grid] = a.g.total_tiles;
+    }
     const int smem = a.g.off_out + a.g.n_strips * a.g.out_bufs * a.g.strip_bytes;
     const int kind = norm == kNormExact ? 0 : (a.g.na_uniform ? 1 : 2);
     cfg->rows_per_tile = a.g.R;
