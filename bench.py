@@ -283,9 +283,6 @@ def run_b200_arm(args):
                 for i in range(n_sets):
                     sets[i].launch_raw(cap.cuda_stream)
         torch.cuda.synchronize(dev)
-        if args.steps % n_sets or args.warmup % n_sets:
-            args.steps = max(n_sets, args.steps // n_sets * n_sets)
-            args.warmup = max(n_sets, -(-args.warmup // n_sets) * n_sets)
 
     def barrier():
         if dist is not None:
@@ -293,23 +290,27 @@ def run_b200_arm(args):
         torch.cuda.synchronize(dev)
 
     sampler = ClockSampler(physical_gpu_index(local_rank))
-    if graph is not None:
-        for _ in range(args.warmup // n_sets):
-            graph.replay()
-    else:
-        for i in range(args.warmup):
-            step(i)
+    def run_steps(first, count):
+        # exactly `count` steps: whole rotations come from the graph, the remainder are plain launches
+        i = 0
+        if graph is not None:
+            while first % n_sets and i < count:  # align to a rotation boundary
+                step(first)
+                first, i = first + 1, i + 1
+            while count - i >= n_sets:
+                graph.replay()
+                first, i = first + n_sets, i + n_sets
+        while i < count:
+            step(first)
+            first, i = first + 1, i + 1
+
+    run_steps(0, args.warmup)
     info = _lib.last_launch_info()
     barrier()
     sampler.start()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record(stream)
-    if graph is not None:
-        for _ in range(args.steps // n_sets):
-            graph.replay()
-    else:
-        for i in range(args.steps):
-            step(args.warmup + i)
+    run_steps(args.warmup, args.steps)
     e1.record(stream)
     barrier()
     clocks = sampler.finish()
@@ -361,59 +362,53 @@ def run_b200_arm(args):
 
 
 def run_e2e(torch, pva_b200, t, wl, dev, dist, world, rank, args):
-    """Public-API path with host buffers: SampleParams -> collate_raw_clips -> GpuPreprocess, then
-    the [slow, fast] result is read back into pinned host memory.  H2D and D2H are inside the
-    timed region, every step."""
+    """Public-API path with HOST buffers.  Every step: worker-side draws (SampleParams) and
+    collate of raw uint8 clips into pinned memory were done up front (they are CPU-worker work
+    in the reference too); inside the timed region each step copies that step's pinned clips to
+    the device, runs the fused kernel, and copies [slow, fast] back into pinned host memory.
+    StagedPreprocess overlaps the three phases of consecutive steps (PCIe is full duplex)."""
     B, shape = wl["batch"], wl["shape"]
     steps = max(5, min(args.steps, args.e2e_steps))
     gen = torch.Generator().manual_seed(99 + rank)
     sp = pva_b200.SampleParams(t)
     host_batches = []
-    for _ in range(2):
+    for _ in range(3):
         samples = [sp({"video": torch.randint(0, 256, shape, dtype=torch.uint8, generator=gen), "label": 0})
                    for _ in range(B)]
         b = pva_b200.collate_raw_clips(samples)
         b["video"] = b["video"].pin_memory()
+        b["params"] = [pva_b200.ClipParams.from_row(r) for r in b["pva_params"].tolist()]
         host_batches.append(b)
-    pre = pva_b200.GpuPreprocess(t, dev)
-    outs_host = None
-    h2d = host_batches[0]["video"].numel()
-    d2h = 0
+    staged = pva_b200.StagedPreprocess(t, B, shape, dev, depth=3, host_out=True)
 
-    def one(i):
-        nonlocal outs_host, d2h
-        batch = dict(host_batches[i % 2])
-        res = pre(batch)["video"]
-        res = res if isinstance(res, list) else [res]
-        # raw memory order (N, T, S, S, C): a flat copy on both sides
-        raws = [r.permute(0, 2, 3, 4, 1) for r in res]
-        if outs_host is None:
-            outs_host = [torch.empty(r.shape, dtype=r.dtype, pin_memory=True) for r in raws]
-            d2h = sum(r.numel() * r.element_size() for r in raws)
-        for h, r in zip(outs_host, raws):
-            h.copy_(r, non_blocking=True)
+    def run(n):
+        tickets = []
+        for i in range(n):
+            hb = host_batches[i % 3]
+            tickets.append(staged.submit(hb["video"], hb["params"]))
+            if len(tickets) > 2:
+                staged.result(tickets[-3])  # consume results in order, two batches in flight
+        for tk in tickets[-2:]:
+            staged.result(tk)
 
-    for i in range(3):
-        one(i)
+    run(4)
+    staged.drain()
     if dist is not None:
         dist.barrier()
     torch.cuda.synchronize(dev)
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     t0 = time.perf_counter()
-    e0.record()
-    for i in range(steps):
-        one(i)
-    e1.record()
+    run(steps)
+    staged.drain()
     torch.cuda.synchronize(dev)
-    wall_ms = (time.perf_counter() - t0) * 1000.0
-    ms = max(e0.elapsed_time(e1), wall_ms)
+    ms = (time.perf_counter() - t0) * 1000.0  # wall clock around fully drained work: includes every copy
     if dist is not None:
         tt = torch.tensor([ms], device=dev, dtype=torch.float64)
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
         ms = float(tt.item())
-    return {"value": world * B * steps / (ms / 1000.0), "unit": UNIT, "h2d_bytes_per_step": int(h2d),
-            "d2h_bytes_per_step": int(d2h), "steps": steps, "ms_per_step": ms / steps,
-            "path": "SampleParams -> collate_raw_clips (pinned) -> GpuPreprocess -> D2H of [slow, fast] (pinned)"}
+    return {"value": world * B * steps / (ms / 1000.0), "unit": UNIT, "h2d_bytes_per_step": int(staged.h2d_bytes),
+            "d2h_bytes_per_step": int(staged.d2h_bytes), "steps": steps, "ms_per_step": ms / steps,
+            "path": "SampleParams -> collate_raw_clips (pinned) -> StagedPreprocess: H2D | fused kernel | D2H of "
+                    "[slow, fast] to pinned memory, 3 slots"}
 
 
 def main():

@@ -28,10 +28,11 @@ from .transforms import (  # noqa: E402
     collate_raw_clips,
     make_transform,
 )
+from .staging import StagedPreprocess  # noqa: E402
 from ._lib import PvaError, library_path, load_library  # noqa: E402
 
 __all__ = [
     "ClipParams", "center_crop_offsets", "pack_indices", "resized_hw", "sample_train_params",
     "temporal_indices", "val_params", "GpuClipTransform", "GpuPreprocess", "PackPathway", "SampleParams",
-    "collate_raw_clips", "make_transform", "PvaError", "library_path", "load_library",
+    "collate_raw_clips", "make_transform", "StagedPreprocess", "PvaError", "library_path", "load_library",
 ]

@@ -1,0 +1,98 @@
+"""Overlapped host -> device -> host staging around the fused kernel.
+
+The reference moves fp32 batches to the device after preprocessing them on the CPU
+(``run.py:196-198``).  Here the raw uint8 batch crosses PCIe instead and the copy is taken
+off the critical path: ``StagedPreprocess`` keeps ``depth`` device-side slots and three
+streams, so that while the kernel works on batch ``i`` the clips of batch ``i+1`` are already
+in flight and -- when the caller asks for host copies of the result -- batch ``i-1`` is on its
+way back.  PCIe is full duplex, so the two copy directions overlap as well.
+
+This is plumbing (torch streams, events and ``copy_``); the arithmetic is the same single
+``pva_preprocess`` launch as everywhere else.
+"""
+from __future__ import annotations
+
+from typing import List, Optional, Sequence
+
+import torch
+
+from .geometry import ClipParams
+from .transforms import GpuClipTransform
+
+
+class _Slot:
+    def __init__(self, t: GpuClipTransform, batch: int, clip_shape: Sequence[int], device: torch.device,
+                 host_out: bool):
+        self.dev_in = torch.empty((batch,) + tuple(clip_shape), dtype=torch.uint8, device=device)
+        self.raw_out = t.alloc_outputs(batch, device)
+        self.host_out = [torch.empty(r.shape, dtype=r.dtype, pin_memory=True) for r in self.raw_out] if host_out else None
+        self.in_ready = torch.cuda.Event()
+        self.kernel_done = torch.cuda.Event()
+        self.out_ready = torch.cuda.Event()
+        self.used = False
+
+
+class StagedPreprocess:
+    """``submit(host_clips, params)`` enqueues H2D + kernel (+ D2H) for one batch and returns a
+    ticket; ``result(ticket)`` waits for that batch only.  ``host_clips`` must be a pinned
+    ``B x C x T x H x W`` uint8 tensor of the shape given at construction."""
+
+    def __init__(self, transform: GpuClipTransform, batch: int, clip_shape: Sequence[int],
+                 device: Optional[torch.device] = None, depth: int = 3, host_out: bool = False):
+        if depth < 2:
+            raise ValueError("depth must be at least 2 to overlap anything")
+        self.t = transform
+        self.device = torch.device(device) if device is not None else torch.device("cuda", torch.cuda.current_device())
+        self.batch = batch
+        self.clip_shape = tuple(clip_shape)
+        self.host_out = host_out
+        self.slots = [_Slot(transform, batch, clip_shape, self.device, host_out) for _ in range(depth)]
+        self.s_in = torch.cuda.Stream(self.device)
+        self.s_run = torch.cuda.Stream(self.device)
+        self.s_out = torch.cuda.Stream(self.device)
+        self._n = 0
+        self.h2d_bytes = self.slots[0].dev_in.numel()
+        self.d2h_bytes = sum(r.numel() * r.element_size() for r in self.slots[0].raw_out) if host_out else 0
+
+    def submit(self, host_clips: torch.Tensor, params: Sequence[ClipParams]) -> int:
+        if tuple(host_clips.shape) != (self.batch,) + self.clip_shape or host_clips.dtype != torch.uint8:
+            raise ValueError(f"expected uint8 clips of shape {(self.batch,) + self.clip_shape}")
+        slot = self.slots[self._n % len(self.slots)]
+        with torch.cuda.stream(self.s_in):
+            if slot.used:
+                self.s_in.wait_event(slot.kernel_done)  # the kernel that read this slot has finished
+            slot.dev_in.copy_(host_clips, non_blocking=True)
+            slot.in_ready.record(self.s_in)
+        with torch.cuda.stream(self.s_run):
+            self.s_run.wait_event(slot.in_ready)
+            if slot.used and self.host_out:
+                self.s_run.wait_event(slot.out_ready)  # the previous result has left the slot
+            prepared = self.t.prepare_batch(slot.dev_in, params, out=slot.raw_out)
+            prepared.launch_raw(self.s_run.cuda_stream)
+            slot.kernel_done.record(self.s_run)
+        if self.host_out:
+            with torch.cuda.stream(self.s_out):
+                self.s_out.wait_event(slot.kernel_done)
+                for h, r in zip(slot.host_out, slot.raw_out):
+                    h.copy_(r, non_blocking=True)
+                slot.out_ready.record(self.s_out)
+        slot.used = True
+        ticket = self._n
+        self._n += 1
+        return ticket
+
+    def result(self, ticket: int) -> List[torch.Tensor]:
+        """Block until batch ``ticket`` is complete.  Returns the pinned host tensors (``host_out=True``,
+        raw ``N x T x S x S x C`` order) or the device tensors as ``[slow, fast]`` logical views."""
+        if ticket < self._n - len(self.slots) or ticket >= self._n:
+            raise ValueError("ticket is no longer (or not yet) resident in a slot")
+        slot = self.slots[ticket % len(self.slots)]
+        if self.host_out:
+            slot.out_ready.synchronize()
+            return slot.host_out
+        slot.kernel_done.synchronize()
+        return [self.t._logical(r) for r in slot.raw_out]
+
+    def drain(self) -> None:
+        for s in (self.s_in, self.s_run, self.s_out):
+            s.synchronize()

@@ -1,0 +1,43 @@
+"""Overlapped staging (host clips -> device -> host) returns the same bytes as a plain call."""
+import pytest
+import torch
+
+import pva_b200
+
+from _util import synth_clip
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("host_out", [False, True])
+def test_staged_pipeline_matches_direct_calls(host_out, cuda_device):
+    kw = dict(min_short_side_scale=128, max_short_side_scale=160, crop_size=128, num_frames=8, training=True)
+    t = pva_b200.make_transform(**kw)
+    shape = (3, 16, 128, 172)
+    staged = pva_b200.StagedPreprocess(t, 4, shape, cuda_device, depth=2, host_out=host_out)
+    torch.manual_seed(3)
+    batches = []
+    for b in range(5):  # more batches than slots: slots are reused
+        clips = torch.stack([synth_clip(shape, 100 * b + i) for i in range(4)]).pin_memory()
+        params = [t.sample_params(128, 172) for _ in range(4)]
+        batches.append((clips, params))
+    tickets = []
+    for i, (clips, params) in enumerate(batches):
+        tickets.append(staged.submit(clips, params))
+        if i >= 1:
+            check(staged, t, tickets[i - 1], batches[i - 1], host_out)
+    check(staged, t, tickets[-1], batches[-1], host_out)
+    with pytest.raises(ValueError):
+        staged.result(tickets[0])  # long gone from its slot
+    staged.drain()
+
+
+def check(staged, t, ticket, batch, host_out):
+    clips, params = batch
+    got = staged.result(ticket)
+    want = t.run_batch(clips.cuda(), params)
+    torch.cuda.synchronize()
+    for g, w in zip(got, want):
+        if host_out:
+            g = g.permute(0, 4, 1, 2, 3)  # raw N x T x S x S x C -> logical
+        assert torch.equal(g.cpu(), w.cpu())
