@@ -29,10 +29,11 @@ from .transforms import (  # noqa: E402
     make_transform,
 )
 from .staging import StagedPreprocess  # noqa: E402
+from .sharding import batches_for_rank, rank_and_world, rank_seed  # noqa: E402
 from ._lib import PvaError, library_path, load_library  # noqa: E402
 
 __all__ = [
     "ClipParams", "center_crop_offsets", "pack_indices", "resized_hw", "sample_train_params",
     "temporal_indices", "val_params", "GpuClipTransform", "GpuPreprocess", "PackPathway", "SampleParams",
-    "collate_raw_clips", "make_transform", "StagedPreprocess", "PvaError", "library_path", "load_library",
+    "collate_raw_clips", "make_transform", "StagedPreprocess", "batches_for_rank", "rank_and_world", "rank_seed", "PvaError", "library_path", "load_library",
 ]
