@@ -59,15 +59,16 @@ typedef enum PvaKernel { PVA_KERNEL_AUTO = 0, PVA_KERNEL_GENERIC = 1, PVA_KERNEL
 
 /* Element type of the source clip.  U8 is what the dataloader hands over; F32 holds the
  * same 0..255 values as floats (what pytorchvideo's decoder produces). */
-typedef enum PvaSrcType { PVA_SRC_U8 = 0 } PvaSrcType;
+typedef enum PvaSrcType { PVA_SRC_U8 = 0, PVA_SRC_F32 = 1 } PvaSrcType;
 
 #define PVA_MAX_CHANNELS 4
 
 /*
  * One clip and its per-clip draws.  Replaces the arguments the reference passes implicitly
  * through the op chain of run.py:81-97:
- *   src, t_in, h, w  : the 'video' entry of the sample dict, uint8 C x T x H x W, contiguous,
- *                      in DEVICE memory
+ *   src, t_in, h, w  : the 'video' entry of the sample dict, C x T x H x W, contiguous, in DEVICE
+ *                      memory; uint8, or float32 when plan->src_type == PVA_SRC_F32 (generic kernel;
+ *                      any float values, evaluated with the reference's two divisions per tap)
  *   frame_idx        : HOST array of plan->n_fast indices into [0, t_in): the result of
  *                      UniformTemporalSubsample's linspace(0, T-1, n).long() (run.py:82).
  *                      Not closed-form in integers, hence a table.  Read during the call only.

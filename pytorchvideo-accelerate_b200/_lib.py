@@ -23,7 +23,7 @@ PVA_F32, PVA_F16, PVA_BF16 = 0, 1, 2
 PVA_LAYOUT_CTHW, PVA_LAYOUT_THWC = 0, 1
 PVA_NORM_EXACT, PVA_NORM_AFFINE = 0, 1
 PVA_KERNEL_AUTO, PVA_KERNEL_GENERIC, PVA_KERNEL_TILED = 0, 1, 2
-PVA_SRC_U8 = 0
+PVA_SRC_U8, PVA_SRC_F32 = 0, 1
 
 EXPORTED_SYMBOLS = (
     "pva_preprocess",

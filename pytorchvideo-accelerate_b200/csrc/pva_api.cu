@@ -107,8 +107,8 @@ int pva_preprocess(const PvaClipDesc* clips, int32_t n_clips, const PvaPlan* pla
         return fail(PVA_ERR_INVALID_ARGUMENT, "norm_mode=%d is not a PvaNormMode", plan->norm_mode);
     if (plan->kernel < PVA_KERNEL_AUTO || plan->kernel > PVA_KERNEL_TILED)
         return fail(PVA_ERR_INVALID_ARGUMENT, "kernel=%d is not a PvaKernel", plan->kernel);
-    if (plan->src_type != PVA_SRC_U8)
-        return fail(PVA_ERR_UNSUPPORTED, "src_type=%d: only uint8 clips are implemented", plan->src_type);
+    if (plan->src_type != PVA_SRC_U8 && plan->src_type != PVA_SRC_F32)
+        return fail(PVA_ERR_INVALID_ARGUMENT, "src_type=%d is not a PvaSrcType", plan->src_type);
     if ((plan->n_slow == 0) != (slow_out == nullptr))
         return fail(PVA_ERR_INVALID_ARGUMENT, "slow_out must be NULL exactly when n_slow == 0 (n_slow=%d)",
                     plan->n_slow);
@@ -149,6 +149,7 @@ int pva_preprocess(const PvaClipDesc* clips, int32_t n_clips, const PvaPlan* pla
     kp.n_fast = plan->n_fast;
     kp.n_slow = plan->n_slow;
     kp.crop = crop;
+    kp.src_f32 = plan->src_type == PVA_SRC_F32 ? 1 : 0;
     kp.fast_clip_elems = (long long)C * plan->n_fast * crop * crop;
     kp.slow_clip_elems = (long long)C * plan->n_slow * crop * crop;
     for (int j = 0; j < plan->n_slow; ++j) kp.slow_idx[j] = (uint16_t)plan->slow_idx[j];
@@ -157,6 +158,8 @@ int pva_preprocess(const PvaClipDesc* clips, int32_t n_clips, const PvaPlan* pla
         if (rc != PVA_OK) return rc;
         for (int c = 0; c < C; ++c) {
             const double m = (double)plan->mean[c], s = (double)plan->std[c];
+            kp.mean[c] = plan->mean[c];
+            kp.std[c] = plan->std[c];
             kp.na[c] = (float)(1.0 / (255.0 * s));
             kp.nb[c] = (float)(-m / s);
         }

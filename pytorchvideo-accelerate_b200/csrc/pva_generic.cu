@@ -10,10 +10,10 @@
 
 namespace pva {
 
-template <typename OutT, int kLayout, int kNorm>
+template <typename OutT, int kLayout, int kNorm, typename SrcT>
 __global__ void __launch_bounds__(256) pva_generic_kernel(const __grid_constant__ KParams p) {
     __shared__ float s_lut[kMaxChannels * 256];
-    if (kNorm == kNormExact) {
+    if (kNorm == kNormExact && sizeof(SrcT) == 1) {
         for (int i = threadIdx.x; i < p.C * 256; i += blockDim.x) s_lut[i] = p.lut[i];
         __syncthreads();
     }
@@ -38,16 +38,27 @@ __global__ void __launch_bounds__(256) pva_generic_kernel(const __grid_constant_
     OutT* slow = p.slow_out ? reinterpret_cast<OutT*>(p.slow_out) + (size_t)clip_i * p.slow_clip_elems : nullptr;
 
     for (int c = 0; c < p.C; ++c) {
-        const uint8_t* plane = g.src + ((size_t)c * g.t_in + t_src) * plane_sz;
-        const uint8_t u00 = __ldg(plane + (size_t)y0 * g.w + x0);
-        const uint8_t u01 = __ldg(plane + (size_t)y0 * g.w + x1);
-        const uint8_t u10 = __ldg(plane + (size_t)y1 * g.w + x0);
-        const uint8_t u11 = __ldg(plane + (size_t)y1 * g.w + x1);
+        const SrcT* plane = reinterpret_cast<const SrcT*>(g.src) + ((size_t)c * g.t_in + t_src) * plane_sz;
+        const SrcT u00 = __ldg(plane + (size_t)y0 * g.w + x0);
+        const SrcT u01 = __ldg(plane + (size_t)y0 * g.w + x1);
+        const SrcT u10 = __ldg(plane + (size_t)y1 * g.w + x0);
+        const SrcT u11 = __ldg(plane + (size_t)y1 * g.w + x1);
         float r;
         if (kNorm == kNormExact) {
-            const float* l = s_lut + c * 256;
-            const float tp = fmaf(lx0, l[u00], lx1 * l[u01]);
-            const float bt = fmaf(lx0, l[u10], lx1 * l[u11]);
+            float v00, v01, v10, v11;
+            if (sizeof(SrcT) == 1) {
+                const float* l = s_lut + c * 256;
+                v00 = l[(int)u00], v01 = l[(int)u01], v10 = l[(int)u10], v11 = l[(int)u11];
+            } else {
+                // float frames: Div255 and Normalize as the reference evaluates them, per tap
+                const float m = p.mean[c], sd = p.std[c];
+                v00 = __fdiv_rn(__fdiv_rn((float)u00, 255.0f) - m, sd);
+                v01 = __fdiv_rn(__fdiv_rn((float)u01, 255.0f) - m, sd);
+                v10 = __fdiv_rn(__fdiv_rn((float)u10, 255.0f) - m, sd);
+                v11 = __fdiv_rn(__fdiv_rn((float)u11, 255.0f) - m, sd);
+            }
+            const float tp = fmaf(lx0, v00, lx1 * v01);
+            const float bt = fmaf(lx0, v10, lx1 * v11);
             r = fmaf(ly0, tp, ly1 * bt);
         } else {
             const float tp = fmaf(lx0, (float)u00, lx1 * (float)u01);
@@ -82,10 +93,13 @@ __global__ void __launch_bounds__(256) pva_generic_kernel(const __grid_constant_
 template <typename OutT>
 static cudaError_t launch_generic_t(const KParams& p, int layout, int norm, cudaStream_t stream, dim3 grid,
                                     dim3 block) {
-#define PVA_GENERIC_CASE(L, N)                                                 \
-    if (layout == L && norm == N) {                                            \
-        pva_generic_kernel<OutT, L, N><<<grid, block, 0, stream>>>(p);         \
-        return cudaGetLastError();                                             \
+#define PVA_GENERIC_CASE(L, N)                                                          \
+    if (layout == L && norm == N) {                                                     \
+        if (p.src_f32)                                                                  \
+            pva_generic_kernel<OutT, L, N, float><<<grid, block, 0, stream>>>(p);       \
+        else                                                                            \
+            pva_generic_kernel<OutT, L, N, uint8_t><<<grid, block, 0, stream>>>(p);     \
+        return cudaGetLastError();                                                      \
     }
     PVA_GENERIC_CASE(kLayoutCTHW, kNormExact)
     PVA_GENERIC_CASE(kLayoutCTHW, kNormAffine)

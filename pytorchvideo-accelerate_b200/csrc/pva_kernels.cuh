@@ -33,11 +33,13 @@ struct KParams {
     void* fast_out;
     void* slow_out;  // nullptr for a single pathway
     int n_clips, C, n_fast, n_slow, crop;
-    int rows_per_tile;  // tiled kernel only
+    int src_f32;        // source clips are float32 (0..255 valued) instead of uint8: generic kernel only
     long long fast_clip_elems;  // C * n_fast * crop * crop
     long long slow_clip_elems;
     float na[kMaxChannels];  // AFFINE: out = fma(p, na, nb), p = bilinear over raw bytes
     float nb[kMaxChannels];
+    float mean[kMaxChannels];  // for float sources, where no table applies
+    float std[kMaxChannels];
     float lut[kMaxChannels * 256];  // EXACT: ((u / 255) - mean) / std, built on the host
     uint16_t frame_idx[kMaxIdxRows][kMaxFrames];  // UniformTemporalSubsample tables (run.py:82)
     uint16_t slow_idx[kMaxFrames];                // PackPathway table (run.py:59-63)

@@ -606,6 +606,10 @@ bool plan_tiles(const KParams& p, int out_dtype, int layout, TileGeom* tg, const
         *why = "tiled kernel handles 3-channel clips";
         return false;
     }
+    if (p.src_f32) {
+        *why = "tiled kernel reads uint8 clips";
+        return false;
+    }
     const int crop = p.crop;
     const int gx = (crop + kPx - 1) / kPx;
     const int tps = round_up(gx, 32);

@@ -137,7 +137,7 @@ class GpuClipTransform:
             tab = self._idx_cache[t_in] = _IdxTable(temporal_indices(t_in, self.num_frames))
         return tab
 
-    def _plan(self) -> _lib.PvaPlan:
+    def _plan(self, src_dtype: torch.dtype = torch.uint8) -> _lib.PvaPlan:
         plan = _lib.PvaPlan()
         plan.channels = len(self.mean)
         plan.n_fast = self.num_frames
@@ -152,7 +152,7 @@ class GpuClipTransform:
         plan.out_layout = _lib.PVA_LAYOUT_THWC if self.channels_last else _lib.PVA_LAYOUT_CTHW
         plan.norm_mode = _NORM[self.norm_mode]
         plan.kernel = _KERNEL[self.kernel]
-        plan.src_type = _lib.PVA_SRC_U8
+        plan.src_type = _lib.PVA_SRC_F32 if src_dtype == torch.float32 else _lib.PVA_SRC_U8
         return plan
 
     def _check_clip(self, video: torch.Tensor) -> None:
@@ -160,8 +160,9 @@ class GpuClipTransform:
             raise TypeError(f"video should be a torch.Tensor, got {type(video)}")
         if video.dim() != 4:
             raise ValueError(f"video should be C x T x H x W, got shape {tuple(video.shape)}")
-        if video.dtype != torch.uint8:
-            raise TypeError(f"video should be uint8 (raw decoded frames), got {video.dtype}")
+        if video.dtype not in (torch.uint8, torch.float32):
+            # uint8 is the raw-frame hand-over; float32 0..255 is what pytorchvideo's decoder produces
+            raise TypeError(f"video should be uint8 or float32 frames in 0..255, got {video.dtype}")
         if video.shape[0] != len(self.mean):
             raise ValueError(f"video has {video.shape[0]} channels, mean/std have {len(self.mean)}")
         if video.numel() == 0:
@@ -201,6 +202,8 @@ class GpuClipTransform:
                 raise ValueError("all clips of a batch must live on one device")
             if not v.is_contiguous():
                 v = v.contiguous()
+            if v.dtype != clip_list[0].dtype:
+                raise TypeError("all clips of a batch must share one dtype")
             keep.append(v)
             _c, t_in, h, w = v.shape
             if p.oh < self.crop_size or p.ow < self.crop_size:
@@ -213,7 +216,7 @@ class GpuClipTransform:
             d.oh, d.ow, d.top, d.left, d.flip = p.oh, p.ow, p.top, p.left, int(p.flip)
         if out is None:
             out = self.alloc_outputs(n, device)
-        return PreparedBatch(self, descs, n, keep, list(out), device)
+        return PreparedBatch(self, descs, n, keep, list(out), device, clip_list[0].dtype)
 
     def run_batch(self, clips: Union[torch.Tensor, Sequence[torch.Tensor]], params: Sequence[ClipParams],
                   out: Optional[Sequence[torch.Tensor]] = None,
@@ -261,14 +264,14 @@ class PreparedBatch:
     """A validated batch: descriptor table, plan and output buffers, ready to (re)launch."""
 
     def __init__(self, transform: GpuClipTransform, descs, n: int, clips: List[torch.Tensor],
-                 out: List[torch.Tensor], device: torch.device):
+                 out: List[torch.Tensor], device: torch.device, src_dtype: torch.dtype = torch.uint8):
         self.t = transform
         self.descs = descs
         self.n = n
         self.clips = clips
         self.raw_out = out
         self.device = device
-        self.plan = transform._plan()
+        self.plan = transform._plan(src_dtype)
         self._plan_ref = ctypes.byref(self.plan)
         self.slow_raw, self.fast_raw = (out[0], out[1]) if transform.n_slow else (None, out[-1])
         self._fast_ptr = self.fast_raw.data_ptr()

@@ -90,7 +90,7 @@ def test_sample_params_and_collate_cpu_side():
 def test_transform_validates_before_any_launch():
     t = pva_b200.make_transform()
     with pytest.raises(TypeError):
-        t({"video": torch.zeros(3, 8, 32, 32)})  # fp32 frames are not raw uint8
+        t({"video": torch.zeros(3, 8, 32, 32, dtype=torch.float64)})  # only uint8 / float32 frames
     with pytest.raises(ValueError):
         t({"video": torch.zeros(8, 32, 32, dtype=torch.uint8)})  # not 4-D
     with pytest.raises(ValueError):

@@ -270,3 +270,24 @@ def test_errors_raise_reference_exception_types(cuda_device):
     with pytest.raises(ValueError, match="crop window"):
         pva_b200.make_transform(crop_size=32, num_frames=4).run_batch(
             [torch.zeros(3, 8, 40, 60, dtype=torch.uint8, device="cuda")], [ClipParams(40, 40, 60, 20, 0, False)])
+
+
+def test_float32_frames_like_the_decoder_hands_over(cuda_device):
+    """pytorchvideo's decoder produces float32 frames in 0..255; the reference ops take them as they
+    are.  The float path evaluates Div255/Normalize per tap with true divisions, so EXACT output is
+    bit-identical to the oracle for any float values, integral or not."""
+    kw = full_kwargs(dict(min_short_side_scale=128, max_short_side_scale=160, crop_size=128, num_frames=8,
+                          training=True))
+    g = torch.Generator().manual_seed(9)
+    for clip in (synth_clip((3, 16, 128, 172), 9).float(), torch.rand((3, 16, 128, 172), generator=g) * 255.0):
+        torch.manual_seed(21)
+        draws = pipeline.replay_draws(128, 172, 128, 160, 128, 0.5)
+        ref = oracle_explicit(clip, draws, kw)
+        t = pva_b200.make_transform(**kw, out_dtype=torch.float32, channels_last=False, norm_mode="exact")
+        out = t.explicit(clip.cuda(), params_from_draws(draws, 128, 172))
+        assert _lib.last_launch_info()["kernel"] == 1  # float sources take the generic kernel
+        for o, r in zip(out, ref):
+            assert np.abs(o.cpu().numpy() - r.numpy()).max() <= 1e-6  # ATen small-frame wobble
+        t16 = pva_b200.make_transform(**kw)
+        for o, r in zip(t16.explicit(clip.cuda(), params_from_draws(draws, 128, 172)), ref):
+            assert np.abs(o.float().cpu().numpy() - r.numpy()).max() <= FP16_TOL
