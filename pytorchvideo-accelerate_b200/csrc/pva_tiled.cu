@@ -62,6 +62,8 @@ struct TileGeom {
     int total_tiles;
     int off_ytab, off_in, off_out, off_lut;
     int pdl;         // launched with programmatic stream serialization
+    int load_rows;   // 1: column-cropped source rows through 128-bit cp.async, one row per producer lane;
+                     // 0: one cp.async.bulk per plane over the full-width row band
     int l2hint;      // bit 0: loads evict_first, bit 1: stores evict_first
     int stages;      // input ring depth (2 or 3)
     int out_bufs;    // staging buffers per strip (2 = double-buffered, 1 = wait before rewriting)
@@ -243,7 +245,9 @@ __global__ void __launch_bounds__(kBlockThreads, 1) pva_tiled_kernel(const __gri
 
     if (tid == 0) {
         for (int s = 0; s < kMaxStages; ++s) {
-            mbar_init(smem_u32(&s_full[s]), 1);  // the producer's arrive.expect_tx; the copies complete the tx count
+            // bulk mode: the producer's arrive.expect_tx, the copies complete the tx count;
+            // row mode: one cp.async-arrive per producer lane
+            mbar_init(smem_u32(&s_full[s]), tg.load_rows ? 32 : 1);
             mbar_init(smem_u32(&s_empty[s]), kConsumerThreads / 32);
         }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -281,7 +285,7 @@ __global__ void __launch_bounds__(kBlockThreads, 1) pva_tiled_kernel(const __gri
                 const ClipGeom& g = p.clips[clip_i];
                 src = g.src, W = g.w, H = g.h, T_in = g.t_in, sy = g.sy, top = g.top, idx_row = g.idx_row;
                 src_range(g.sx, g.left, g.left + crop - 1, g.w, ca, ncols);
-                pitch = W;
+                pitch = tg.load_rows ? tg.pitch0 + ((W - tg.pitch0) & 15) : W;
             }
             const int yb = band * tg.R;
             const int ye = min(yb + tg.R, crop);
@@ -291,25 +295,48 @@ __global__ void __launch_bounds__(kBlockThreads, 1) pva_tiled_kernel(const __gri
             const int t_src = p.frame_idx[idx_row][k];
             const uint32_t st_base = in_base + (uint32_t)s * tg.stage_bytes;
             const uint32_t bar = smem_u32(&s_full[s]);
-            // One bulk copy per plane: the whole band of source rows, first needed byte (ra, ca) to
-            // last needed byte, rounded out to 16-byte granules.  Rows are contiguous in memory, so
-            // this is a single linear range; staged byte (r, col) sits at
-            //   plane base + (g0 & 15) + (r - ra) * W + (col - ca).
-            const uint8_t* g0 = src + (((size_t)min(lane, 2) * T_in + t_src) * H + ra) * W + ca;
-            const uint32_t sh = (uint32_t)((uintptr_t)g0 & 15);
-            const uint32_t bytes = (sh + (uint32_t)(nrows - 1) * (uint32_t)W + (uint32_t)ncols + 15u) & ~15u;
-            uint32_t total = lane < 3 ? bytes : 0u;
-            total += __shfl_xor_sync(0xffffffffu, total, 1);
-            total += __shfl_xor_sync(0xffffffffu, total, 2);
-            if (tg.debug & 2) total = 0;
-            if (lane == 0) mbar_arrive_expect_tx(bar, total);
-            __syncwarp();
-            if (lane < 3 && !(tg.debug & 2)) {
-                if (tg.l2hint & 1) bulk_load_hint(st_base + (uint32_t)lane * tg.plane_stride, g0 - sh, bytes, bar, pol);
-                else bulk_load(st_base + (uint32_t)lane * tg.plane_stride, g0 - sh, bytes, bar);
+            if (tg.load_rows) {
+                // Column-cropped rows, one source row per lane and pass: each lane walks its row in
+                // 16-byte granules (global and shared side both aligned because pitch == W mod 16).
+                // Staged byte (rr, col) sits at plane base + (gc & 15) + rr * pitch + (col - ca).
+                if (!(tg.debug & 2)) {
+                    const int n_rows_all = 3 * nrows;
+                    for (int j = lane; j < n_rows_all; j += 32) {
+                        const int c = j / nrows, rr = j - c * nrows;
+                        const uint8_t* gc = src + (((size_t)c * T_in + t_src) * H + ra) * W + ca;
+                        const uint8_t* ga = gc + (size_t)rr * W;
+                        const uint32_t sh = (uint32_t)((uintptr_t)ga & 15);
+                        const int n16 = (int)((sh + ncols + 15) >> 4);  // granules holding a needed byte
+                        const uint8_t* al = ga - sh;
+                        uint32_t dst = st_base + (uint32_t)c * tg.plane_stride + (uint32_t)((uintptr_t)gc & 15) +
+                                       (uint32_t)rr * pitch - sh;
+#pragma unroll 4
+                        for (int q = 0; q < n16; ++q) cp_async16(dst + 16 * q, al + 16 * q);
+                    }
+                }
+                cp_async_arrive(bar);
+            } else {
+                // One bulk copy per plane: the whole band of source rows, first needed byte (ra, ca)
+                // to last needed byte, rounded out to 16-byte granules.  Rows are contiguous in
+                // memory, so this is a single linear range; staged byte (r, col) sits at
+                //   plane base + (g0 & 15) + (r - ra) * W + (col - ca).
+                const uint8_t* g0 = src + (((size_t)min(lane, 2) * T_in + t_src) * H + ra) * W + ca;
+                const uint32_t sh = (uint32_t)((uintptr_t)g0 & 15);
+                const uint32_t bytes = (sh + (uint32_t)(nrows - 1) * (uint32_t)W + (uint32_t)ncols + 15u) & ~15u;
+                uint32_t total = lane < 3 ? bytes : 0u;
+                total += __shfl_xor_sync(0xffffffffu, total, 1);
+                total += __shfl_xor_sync(0xffffffffu, total, 2);
+                if (tg.debug & 2) total = 0;
+                if (lane == 0) mbar_arrive_expect_tx(bar, total);
+                __syncwarp();
+                if (lane < 3 && !(tg.debug & 2)) {
+                    if (tg.l2hint & 1) bulk_load_hint(st_base + (uint32_t)lane * tg.plane_stride, g0 - sh, bytes, bar, pol);
+                    else bulk_load(st_base + (uint32_t)lane * tg.plane_stride, g0 - sh, bytes, bar);
+                }
             }
             if (++s == n_stages) s = 0, ph ^= 1u;
         }
+        if (tg.load_rows) asm volatile("cp.async.wait_all;" ::: "memory");  // no copy may outlive the CTA
         return;
     }
 
@@ -353,7 +380,8 @@ __global__ void __launch_bounds__(kBlockThreads, 1) pva_tiled_kernel(const __gri
             cur_clip = clip_i;
             const ClipGeom& g = p.clips[clip_i];
             src = g.src, W = g.w, H = g.h, T_in = g.t_in, idx_row = g.idx_row;
-            pitch = W;  // the staged band is a linear image of the source rows
+            // staged pitch: the source pitch itself (band copies) or the cropped pitch congruent to it mod 16
+            pitch = tg.load_rows ? tg.pitch0 + ((W - tg.pitch0) & 15) : W;
             // AFFINE: the row weights absorb the 2^24 of the subnormal trick and, when all
             // channels share it, the normalisation scale 1 / (255 std)
             const float wscale = (kNorm == kNormAffine) ? 16777216.0f * (kUniformNa ? p.na[0] : 1.0f) : 1.0f;
@@ -630,7 +658,10 @@ bool plan_tiles(const KParams& p, int out_dtype, int layout, TileGeom* tg, const
         host_taps(g.sx, g.left + crop - 1, g.w, &b0, &b1);
         max_cols = max_cols > (b1 - a0 + 1) ? max_cols : (b1 - a0 + 1);
     }
-    const int pitch0 = 0;  // unused: staged rows keep the source pitch
+    const int load_rows = env_int("PVA_TILED_LOAD_ROWS", 0);
+    // row mode: rows of a staged plane must not overlap; a copy spills up to 15 bytes on either side
+    const int pitch0 = max_cols + 15;
+    const int pitch_max = pitch0 + 15;
     const int ytab_bytes = round_up(crop * 16, 128);
     const int lut_bytes = 3 * 256 * 4;
     const bool bulk_ok = (row_bytes % 16) == 0 && ((uintptr_t)p.fast_out % 16 == 0) &&
@@ -666,7 +697,7 @@ bool plan_tiles(const KParams& p, int out_dtype, int layout, TileGeom* tg, const
             }
         }
         // + 15 leading alignment bytes, rounded to a granule, + the 8-byte tap window overhang
-        const int plane_stride = round_up(band_bytes + 15 + 16 + 8, 16);
+        const int plane_stride = load_rows ? round_up(rows_cap * pitch_max + 48, 16) : round_up(band_bytes + 15 + 16 + 8, 16);
         const int stage_bytes = round_up(3 * plane_stride, 128);
         const int strip_bytes = round_up(rps * row_bytes, 128);
         int off = 0;
@@ -687,6 +718,7 @@ bool plan_tiles(const KParams& p, int out_dtype, int layout, TileGeom* tg, const
         tg->bands = bands;
         tg->rows_cap = rows_cap;
         tg->pitch0 = pitch0;
+        tg->load_rows = load_rows;
         tg->plane_stride = plane_stride;
         tg->stage_bytes = stage_bytes;
         tg->strip_bytes = strip_bytes;

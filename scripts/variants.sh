@@ -1,12 +1,10 @@
 #!/bin/bash
-# A/B of launch-level switches on the default workload (graph and plain launches)
+# A/B of launch-level switches on the default workload
 run() { python bench.py $2 --steps 3000 --warmup 40 --no-cpu-baseline --e2e-steps 5 2>/dev/null | python -c "
-import json,sys; d=json.loads(sys.stdin.read()); print('$1 $2', round(d['ms_per_step']*1000,1),'us')"; }
-for g in "--graph" ""; do
-PVA_TILED_PDL=0 run "pdl=0" "$g"
-PVA_TILED_PDL=1 run "pdl=1" "$g"
-PVA_TILED_L2HINT=1 run "pdl=1 hint=1" "$g"
-PVA_TILED_L2HINT=2 run "pdl=1 hint=2" "$g"
-PVA_TILED_L2HINT=3 run "pdl=1 hint=3" "$g"
-PVA_TILED_PDL=0 run "pdl=0 again" "$g"
-done
+import json,sys; d=json.loads(sys.stdin.read()); print('$1 $2', round(d['ms_per_step']*1000,1),'us', d['config']['launch']['smem_bytes'])"; }
+PVA_TILED_LOAD_ROWS=0 run "bulk-band loads"
+PVA_TILED_LOAD_ROWS=1 run "row loads"
+PVA_TILED_LOAD_ROWS=1 PVA_TILED_DEBUG=5 run "row loads, loads only"
+PVA_TILED_LOAD_ROWS=1 PVA_TILED_DEBUG=4 run "row loads, no arithmetic"
+PVA_TILED_LOAD_ROWS=0 PVA_TILED_DEBUG=4 run "bulk loads, no arithmetic"
+PVA_TILED_LOAD_ROWS=1 PVA_TILED_STAGES=3 PVA_TILED_OUTBUFS=3 run "row loads 3 stages"
