@@ -242,6 +242,8 @@ def run_b200_arm(args):
     wl = dict(WORKLOADS[args.workload])
     if args.batch:
         wl["batch"] = args.batch  # experiments only; the named workloads define the reported metric
+    if args.size:
+        wl["kwargs"] = dict(wl["kwargs"], min_short_side_scale=args.size, max_short_side_scale=args.size)
     B, shape, kw = wl["batch"], wl["shape"], wl["kwargs"]
     t = pva_b200.make_transform(**kw, device=dev, out_dtype=torch.float16, channels_last=True,
                                 norm_mode=args.norm_mode, kernel=args.kernel)
@@ -424,6 +426,7 @@ def main():
     ap.add_argument("--cpu-seconds", dest="cpu_seconds", type=float, default=12.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--batch", type=int, default=0, help="override the workload's batch (experiments)")
+    ap.add_argument("--size", type=int, default=0, help="fix the short-side scale (bandwidth sweep)")
     ap.add_argument("--graph", dest="graph", action="store_true", default=True,
                     help="replay the steps from a captured CUDA graph (default)")
     ap.add_argument("--no-graph", dest="graph", action="store_false", help="plain launches through the C ABI")
