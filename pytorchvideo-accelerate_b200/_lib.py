@@ -89,7 +89,9 @@ _LIB: Optional[ctypes.CDLL] = None
 
 
 def library_path() -> str:
-    return os.path.join(os.path.dirname(os.path.abspath(__file__)), "libpva_preproc.so")
+    """The in-tree library; PVA_LIBRARY points at another build of the same ABI (kernel A/B runs)."""
+    return os.environ.get("PVA_LIBRARY") or os.path.join(os.path.dirname(os.path.abspath(__file__)),
+                                                         "libpva_preproc.so")
 
 
 def load_library() -> ctypes.CDLL:

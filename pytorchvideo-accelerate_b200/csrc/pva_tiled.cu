@@ -603,7 +603,8 @@ __global__ void __launch_bounds__(kBlockThreads, 1) pva_tiled_kernel(const __gri
             }
         }
     }
-    if (tg.bulk_store && g_col == 0 && in_strip) bulk_wait_all();
+    // the staging buffers must outlive the stores' reads; the writes themselves complete with the kernel
+    if (tg.bulk_store && g_col == 0 && in_strip) bulk_wait_read_all();
 }
 
 int round_up(int v, int m) { return (v + m - 1) / m * m; }
