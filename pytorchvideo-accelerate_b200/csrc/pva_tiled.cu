@@ -40,7 +40,14 @@ namespace pva {
 namespace {
 
 constexpr int kConsumerThreads = 512;
-constexpr int kBlockThreads = kConsumerThreads + 32;
+// 16 consumer warps + one producer WARPGROUP (only its first warp works): setmaxnreg trades
+// registers between the roles in warpgroup units, which lets the consumers have 112 registers
+// although 20 warps x 96 is all the register file holds at launch.  setmaxnreg.inc draws only on
+// what setmaxnreg.dec released inside the CTA: 4 warps x 32 x (96 - 24) = 9216 registers released,
+// 16 warps x 32 x (112 - 96) = 8192 claimed (were it more, the consumers would wait forever).
+constexpr int kBlockThreads = kConsumerThreads + 128;
+constexpr int kProducerRegs = 24, kConsumerRegs = 112;
+static_assert(4 * (96 - kProducerRegs) >= 16 * (kConsumerRegs - 96), "consumers would wait forever for registers");
 constexpr int kMaxStages = 3;
 constexpr int kMaxStrips = 8;  // named barriers 1..8 (15 is the consumer-wide one)
 constexpr int kMaxSmem = 227 * 1024;
@@ -51,7 +58,8 @@ struct TileGeom {
     int R;          // output rows per tile
     int rps;        // rows per strip
     int tps;        // threads per strip (multiple of 32)
-    int n_strips;
+    int n_strips;   // strips per consumer group
+    int groups;     // consumer groups (1 or 2); group g takes this CTA's tiles t_begin + g, + groups, ...
     int bands;      // ceil(crop / R)
     int rows_cap;   // source rows per plane a stage can hold
     int pitch0;     // minimum staged row pitch; a clip uses pitch0 + ((w - pitch0) & 15) so that pitch == w (mod 16)
@@ -232,7 +240,10 @@ __global__ void __launch_bounds__(kBlockThreads, 1) pva_tiled_kernel(const __gri
     constexpr bool kUniformNa = kNormT == 1;
     const KParams& p = a.p;
     const TileGeom& tg = a.g;
-    __shared__ __align__(8) unsigned long long s_full[kMaxStages];
+    // one "tile has landed" barrier per (stage, consumer group): with an odd ring depth a stage
+    // alternates between the groups, and a group polling a shared barrier by parity could run two
+    // phases ahead of it (bulk copies complete out of order) and take the other group's phase for its own
+    __shared__ __align__(8) unsigned long long s_full[kMaxStages * 2];
     __shared__ __align__(8) unsigned long long s_empty[kMaxStages];
 
     const int tid = threadIdx.x;
@@ -244,11 +255,11 @@ __global__ void __launch_bounds__(kBlockThreads, 1) pva_tiled_kernel(const __gri
     const int tiles_per_clip = p.n_fast * tg.bands;
 
     if (tid == 0) {
-        for (int s = 0; s < kMaxStages; ++s) {
+        for (int s = 0; s < kMaxStages * 2; ++s) {
             // bulk mode: the producer's arrive.expect_tx, the copies complete the tx count;
             // row mode: one cp.async-arrive per producer lane
             mbar_init(smem_u32(&s_full[s]), tg.load_rows ? 32 : 1);
-            mbar_init(smem_u32(&s_empty[s]), kConsumerThreads / 32);
+            if (s < kMaxStages) mbar_init(smem_u32(&s_empty[s]), kConsumerThreads / 32 / tg.groups);  // the warps of the group that consumed the tile
         }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
@@ -268,6 +279,8 @@ __global__ void __launch_bounds__(kBlockThreads, 1) pva_tiled_kernel(const __gri
 
     if (tid >= kConsumerThreads) {
         // ------------------------------ producer warp ------------------------------
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(kProducerRegs));
+        if (tid >= kConsumerThreads + 32) return;  // the other three warps only existed to give registers away
         const int lane = tid - kConsumerThreads;
         const uint64_t pol = l2_evict_first_policy();
         int cur_clip = -1, ca = 0, ncols = 0, W = 0, H = 0, T_in = 0, pitch = 0, top = 0, idx_row = 0;
@@ -276,6 +289,7 @@ __global__ void __launch_bounds__(kBlockThreads, 1) pva_tiled_kernel(const __gri
         int s = 0;
         uint32_t ph = 0;
         for (int t = t_begin; t < t_end; ++t) {
+            const int grp = (t - t_begin) % tg.groups;  // the consumer group this tile is for
             const int clip_i = t / tiles_per_clip;
             const int rem = t - clip_i * tiles_per_clip;
             const int k = rem / tg.bands;
@@ -294,7 +308,7 @@ __global__ void __launch_bounds__(kBlockThreads, 1) pva_tiled_kernel(const __gri
             mbar_wait(smem_u32(&s_empty[s]), ph ^ 1u);
             const int t_src = p.frame_idx[idx_row][k];
             const uint32_t st_base = in_base + (uint32_t)s * tg.stage_bytes;
-            const uint32_t bar = smem_u32(&s_full[s]);
+            const uint32_t bar = smem_u32(&s_full[2 * s + grp]);
             if (tg.load_rows) {
                 // Column-cropped rows, one source row per lane and pass: each lane walks its row in
                 // 16-byte granules (global and shared side both aligned because pitch == W mod 16).
@@ -341,15 +355,24 @@ __global__ void __launch_bounds__(kBlockThreads, 1) pva_tiled_kernel(const __gri
     }
 
     // -------------------------------- consumers --------------------------------
-    const int strip = tid / tg.tps;
-    const int g_col = tid - strip * tg.tps;  // column group of this thread
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(kConsumerRegs));
+    // Two consumer groups alternate over the CTA's tiles: each gives its strips twice the rows of
+    // a tile (more reuse of the x-pass, half the per-tile set-up per warp), and while one group
+    // waits -- for its tile to land or for its single staging slot to drain -- the other computes.
+    const int group_threads = kConsumerThreads / tg.groups;
+    const int group = tid / group_threads;
+    const int gtid = tid - group * group_threads;
+    const int strip = gtid / tg.tps;          // strip index inside the group
+    const int g_col = gtid - strip * tg.tps;  // column group of this thread
     const int gx = (crop + kPx - 1) / kPx;
     const bool in_strip = strip < tg.n_strips;
+    const int bar_strip = 1 + group * tg.n_strips + strip;  // named barrier of this strip (1..8)
+    const int bar_group = 15 - group;                       // named barrier of this consumer group
     const bool active_col = g_col < gx && in_strip;
     const bool full_group = (kPx * g_col + kPx) <= crop && (crop & 3) == 0;  // vector staging stores need crop % 4 == 0
     const int strip_threads = tg.tps;
-    int4* ytab = reinterpret_cast<int4*>(smem + tg.off_ytab);
-    unsigned char* out_base = smem + tg.off_out + (size_t)strip * tg.out_bufs * tg.strip_bytes;
+    int4* ytab = reinterpret_cast<int4*>(smem + tg.off_ytab) + (size_t)group * crop;  // one row table per group
+    unsigned char* out_base = smem + tg.off_out + (size_t)(group * tg.n_strips + strip) * tg.out_bufs * tg.strip_bytes;
     const float* lut = reinterpret_cast<const float*>(smem + tg.off_lut);
     const size_t esz = sizeof(OutT);
 
@@ -365,18 +388,21 @@ __global__ void __launch_bounds__(kBlockThreads, 1) pva_tiled_kernel(const __gri
     for (int i = 0; i < kPx; ++i) off0[i] = off1[i] = 0, lx0[i] = lx1[i] = 0.f;
 
     int strip_it = 0;  // staging buffer index of this strip
-    int s = 0;
-    uint32_t ph = 0;
 
-    for (int t = t_begin; t < t_end; ++t) {
+    for (int t = t_begin + group; t < t_end; t += tg.groups) {
+        const int it = t - t_begin;
+        const int s = it % n_stages;  // input stage of this tile
+        // its (stage, group) barrier completes once every `period` tiles
+        const int period = (n_stages % tg.groups == 0) ? n_stages : n_stages * tg.groups;
+        const uint32_t ph = (uint32_t)(it / period) & 1u;
         const int clip_i = t / tiles_per_clip;
         const int rem = t - clip_i * tiles_per_clip;
         const int k = rem / tg.bands;
         const int band = rem - k * tg.bands;
 
         if (clip_i != cur_clip) {
-            // every strip must have left the previous clip before the row table is rebuilt
-            named_bar(15, kConsumerThreads);
+            // every strip of the group must have left the previous clip before its row table is rebuilt
+            named_bar(bar_group, group_threads);
             cur_clip = clip_i;
             const ClipGeom& g = p.clips[clip_i];
             src = g.src, W = g.w, H = g.h, T_in = g.t_in, idx_row = g.idx_row;
@@ -385,7 +411,7 @@ __global__ void __launch_bounds__(kBlockThreads, 1) pva_tiled_kernel(const __gri
             // AFFINE: the row weights absorb the 2^24 of the subnormal trick and, when all
             // channels share it, the normalisation scale 1 / (255 std)
             const float wscale = (kNorm == kNormAffine) ? 16777216.0f * (kUniformNa ? p.na[0] : 1.0f) : 1.0f;
-            for (int y = tid; y < crop; y += kConsumerThreads) {
+            for (int y = gtid; y < crop; y += group_threads) {
                 int y0, y1;
                 float l0, l1;
                 bilinear_taps(g.sy, g.top + y, g.h, y0, y1, l0, l1);
@@ -412,7 +438,7 @@ __global__ void __launch_bounds__(kBlockThreads, 1) pva_tiled_kernel(const __gri
                 sel0 |= (uint32_t)((x0v[i] - wc) & 7) << (4 * i);
                 sel1 |= (uint32_t)((x1v[i] - wc) & 7) << (4 * i);
             }
-            named_bar(15, kConsumerThreads);
+            named_bar(bar_group, group_threads);
         }
 
         const int yb = band * tg.R;
@@ -425,11 +451,11 @@ __global__ void __launch_bounds__(kBlockThreads, 1) pva_tiled_kernel(const __gri
         if (tg.out_bufs == 1 && tg.bulk_store && in_strip) {
             // single staging buffer: the previous tile's store must have drained it
             if (g_col == 0) bulk_wait_read_all();
-            named_bar(1 + strip, strip_threads);
+            named_bar(bar_strip, strip_threads);
         }
 
         // every thread polls: measured faster than one poller per warp + __syncwarp (43.4 vs 46.0 us)
-        mbar_wait(smem_u32(&s_full[s]), ph);
+        mbar_wait(smem_u32(&s_full[2 * s + group]), ph);
 
         if (active_col && rows > 0 && !(tg.debug & 4)) {
             const int ra = ytab[yb].x;  // first source row staged for this tile
@@ -553,7 +579,6 @@ __global__ void __launch_bounds__(kBlockThreads, 1) pva_tiled_kernel(const __gri
         // this warp no longer reads the input stage
         __syncwarp();
         if ((tid & 31) == 0) mbar_arrive(smem_u32(&s_empty[s]));
-        if (++s == n_stages) s = 0, ph ^= 1u;
 
         if (in_strip) {
             // ---- strip store: staging -> global (fast pathway, and slow when frame k belongs to it)
@@ -567,7 +592,7 @@ __global__ void __launch_bounds__(kBlockThreads, 1) pva_tiled_kernel(const __gri
                     if (tg.out_bufs == 2) bulk_wait_read_all();
                     if (tg.out_bufs == 3) bulk_wait_read_but_one();  // the store before last has drained
                 }
-                named_bar(1 + strip, strip_threads);
+                named_bar(bar_strip, strip_threads);
                 if (g_col == 0 && rows > 0 && !(tg.debug & 1)) {
                     const uint32_t ssrc = smem_u32(stage_out);
                     const uint32_t bytes = (uint32_t)((size_t)rows * crop * 3 * esz);
@@ -589,7 +614,7 @@ __global__ void __launch_bounds__(kBlockThreads, 1) pva_tiled_kernel(const __gri
                 if (++strip_it >= tg.out_bufs) strip_it = 0;
             } else {
                 // alignment does not allow bulk stores: cooperative element copy by the strip
-                named_bar(1 + strip, strip_threads);
+                named_bar(bar_strip, strip_threads);
                 const OutT* st = reinterpret_cast<const OutT*>(stage_out);
                 const int n_el = rows * crop * 3;
                 for (int idx = g_col; idx < n_el; idx += strip_threads) {
@@ -599,7 +624,7 @@ __global__ void __launch_bounds__(kBlockThreads, 1) pva_tiled_kernel(const __gri
                         for (int j = 0; j < p.n_slow; ++j)
                             if (p.slow_idx[j] == k) slow[((size_t)j * crop + y_begin) * crop * 3 + idx] = v;
                 }
-                named_bar(1 + strip, strip_threads);  // staging may be overwritten by the next tile
+                named_bar(bar_strip, strip_threads);  // staging may be overwritten by the next tile
             }
         }
     }
@@ -646,8 +671,8 @@ bool plan_tiles(const KParams& p, int out_dtype, int layout, TileGeom* tg, const
         *why = "crop wider than 2048";
         return false;
     }
-    int n_strips = kConsumerThreads / tps;
-    if (n_strips > kMaxStrips) n_strips = kMaxStrips;
+    int strips_total = kConsumerThreads / tps;  // over all consumer groups
+    if (strips_total > kMaxStrips) strips_total = kMaxStrips;
     const int esz = out_dtype == 0 ? 4 : 2;
     const int row_bytes = crop * 3 * esz;
 
@@ -663,20 +688,25 @@ bool plan_tiles(const KParams& p, int out_dtype, int layout, TileGeom* tg, const
     // row mode: rows of a staged plane must not overlap; a copy spills up to 15 bytes on either side
     const int pitch0 = max_cols + 15;
     const int pitch_max = pitch0 + 15;
-    const int ytab_bytes = round_up(crop * 16, 128);
     const int lut_bytes = 3 * 256 * 4;
     const bool bulk_ok = (row_bytes % 16) == 0 && ((uintptr_t)p.fast_out % 16 == 0) &&
                          (!p.slow_out || (uintptr_t)p.slow_out % 16 == 0);
 
-    // candidate configurations in order of preference: (rows per strip, stages, staging buffers)
-    static const int kCand[][3] = {{8, 2, 1}, {4, 2, 3}, {4, 3, 2}, {4, 2, 2}, {4, 2, 1}, {2, 3, 2}, {2, 2, 2}, {2, 2, 1}, {1, 2, 2}, {1, 2, 1}};
+    // candidate configurations in order of preference:
+    // (consumer groups, rows per strip, input stages, staging buffers per strip)
+    static const int kCand[][4] = {{2, 8, 3, 1}, {1, 4, 2, 3}, {1, 4, 3, 2}, {1, 4, 2, 2}, {1, 4, 2, 1}, {1, 2, 3, 2},
+                                   {1, 2, 2, 2}, {1, 2, 2, 1}, {1, 1, 2, 2}, {1, 1, 2, 1}};
     const int force_rps = env_int("PVA_TILED_RPS", 0), force_bufs = env_int("PVA_TILED_OUTBUFS", 0),
-              force_stages = env_int("PVA_TILED_STAGES", 0);
+              force_stages = env_int("PVA_TILED_STAGES", 0), force_groups = env_int("PVA_TILED_GROUPS", 0);
     for (const auto& cand : kCand) {
-        const int rps = cand[0], stages = cand[1], out_bufs = bulk_ok ? cand[2] : 1;
+        const int groups = cand[0], rps = cand[1], stages = cand[2], out_bufs = bulk_ok ? cand[3] : 1;
+        if (force_groups && groups != force_groups) continue;
         if (force_rps && rps != force_rps) continue;
-        if (force_bufs && cand[2] != force_bufs) continue;
+        if (force_bufs && cand[3] != force_bufs) continue;
         if (force_stages && stages != force_stages) continue;
+        if (groups == 2 && (strips_total < 2 || strips_total % 2 || !bulk_ok)) continue;
+        const int n_strips = strips_total / groups;  // per group
+        const int ytab_bytes = round_up(groups * crop * 16, 128);
         const int R = rps * n_strips;
         const int bands = (crop + R - 1) / R;
         int rows_cap = 0, band_bytes = 0;
@@ -710,8 +740,9 @@ bool plan_tiles(const KParams& p, int out_dtype, int layout, TileGeom* tg, const
         tg->off_in = off;
         off += stages * stage_bytes;
         tg->off_out = off;
-        off += n_strips * out_bufs * strip_bytes;
+        off += groups * n_strips * out_bufs * strip_bytes;
         if (off + 1024 > kMaxSmem) continue;
+        tg->groups = groups;
         tg->R = R;
         tg->rps = rps;
         tg->tps = tps;
@@ -815,7 +846,7 @@ cudaError_t launch_tiled(KParams& p, int out_dtype, int layout, int norm, cudaSt
         }
         a.tile_begin[grid] = a.g.total_tiles;
     }
-    const int smem = a.g.off_out + a.g.n_strips * a.g.out_bufs * a.g.strip_bytes;
+    const int smem = a.g.off_out + a.g.groups * a.g.n_strips * a.g.out_bufs * a.g.strip_bytes;
     const int kind = norm == kNormExact ? 0 : (a.g.na_uniform ? 1 : 2);
     cfg->rows_per_tile = a.g.R;
     cfg->smem_bytes = smem;
