@@ -1,31 +1,32 @@
 // pva_tiled.cu -- the production kernel: persistent, warp-specialised, bulk-copy staged.
 //
 // Work item ("tile") = (clip, fast frame k, band of R output rows), all C=3 channels.
-// Per tile:
-//   producer warp  : 128-bit cp.async (LDGSTS) of the source row segments the band touches,
-//                    three planes, into a shared-memory stage; completion on an mbarrier
-//                    (cp.async.mbarrier.arrive).  Per-row cp.async.bulk copies were measured at
-//                    ~90 cycles per 256-byte row on the SM's TMA unit -- 57 us for the loads
-//                    alone -- so the row segments go through LDGSTS and TMA is kept for the
-//                    large contiguous stores.  Temporal subsampling (run.py:82) is folded into
-//                    the source address.
-//   consumer warps : each thread owns 4 adjacent output columns x 3 channels.  The x-pass is
-//                    computed once per SOURCE row (two aligned 32-bit shared loads per plane,
-//                    taps picked with PRMT, bytes turned into floats as fp16 subnormals: a
-//                    zero-extended byte IS the half b * 2^-24) and kept in registers; consecutive output rows
-//                    reuse it for the y-pass (bilinear, run.py:89/95).  Crop and flip
-//                    (run.py:90-91) are folded into the per-thread column tables, Div255 +
-//                    Normalize (run.py:83-84) into the epilogue (AFFINE) or a table (EXACT).
+// One CTA per SM, each with a contiguous share of the tiles.  Per tile:
+//   producer warp  : one cp.async.bulk (TMA, 1-D) per channel plane over the whole band of source
+//                    rows the tile touches (rows are contiguous, so a band is one linear range),
+//                    into a stage of a 3-deep shared-memory ring; completion on an mbarrier.
+//                    Temporal subsampling (run.py:82) is folded into the source address.
+//                    Measured alternatives: per-row bulk copies (~90 cycles per 256-byte row on
+//                    the SM's TMA unit: 57 us for the loads alone) and LDGSTS producers (slower).
+//   consumer warps : 16 warps in two groups of 8 that alternate over the tiles.  A group's four
+//                    strips take 8 output rows each; each thread owns 4 adjacent output columns x
+//                    3 channels.  The x-pass is computed once per SOURCE row (two aligned 32-bit
+//                    shared loads per plane, taps picked with PRMT, bytes turned into floats as
+//                    fp16 subnormals: a zero-extended byte IS the half b * 2^-24) and kept in
+//                    registers; consecutive output rows reuse it for the y-pass (bilinear,
+//                    run.py:89/95).  Crop and flip (run.py:90-91) are folded into the per-thread
+//                    column tables, Div255 + Normalize (run.py:83-84) into the epilogue (AFFINE)
+//                    or a table (EXACT).
 //   store          : outputs are packed to fp16/bf16/fp32 into a shared staging strip in final
 //                    memory order and written with cp.async.bulk shared->global: once to the
 //                    fast pathway and again to the slow pathway when the frame belongs to it
 //                    (PackPathway, run.py:59-63) -- the source is read once.
 //
-// The source row pitch (340 B) is not a multiple of 16, so a 2-D tensor map is not legal; each
-// row segment is copied from its 16-byte-aligned superset.  The staged pitch is chosen congruent
-// to the source pitch modulo 16, which makes the staged address of (row, column) LINEAR in the
-// row index although every row starts at a different 16-byte phase: no per-row shift to compute.
+// The source row pitch (340 B) is not a multiple of 16, so a 2-D tensor map is not legal.  The
+// staged band keeps the source pitch and starts at the 16-byte granule of its first needed byte,
+// which makes the staged address of (row, column) LINEAR in the row index: no per-row shift.
 // The library only ever reads 16-byte granules that contain at least one byte of the clip.
+// (PVA_TILED_LOAD_ROWS=1 selects an experimental column-cropped LDGSTS load path; measured slower.)
 //
 // Layout: this kernel writes T x S x S x C (channels-last) only; the reference's C x T x S x S
 // order is served by the generic kernel.
