@@ -382,7 +382,13 @@ def run_e2e(torch, pva_b200, t, wl, dev, dist, world, rank, args):
         b["params"] = [pva_b200.ClipParams.from_row(r) for r in b["pva_params"].tolist()]
         host_batches.append(b)
     def measure(host_out):
-        staged = pva_b200.StagedPreprocess(t, B, shape, dev, depth=3, host_out=host_out)
+        # Strided selected-frame upload halves the H2D bytes, but its many 2-D copies overlap worse
+        # with a concurrent full-size D2H stream than one flat copy does (3.13 vs 2.82 ms per step
+        # measured), so the host-to-host figure uploads whole clips; when the result stays on the
+        # device (no D2H leg) the selected-frame upload is what pays (1.40 vs 2.41 ms).
+        selected = (not host_out) and not args.upload_all_frames
+        staged = pva_b200.StagedPreprocess(t, B, shape, dev, depth=3, host_out=host_out,
+                                           upload_selected_frames=selected)
 
         def run(n):
             tickets = []
@@ -411,15 +417,18 @@ def run_e2e(torch, pva_b200, t, wl, dev, dist, world, rank, args):
         return ms, staged.h2d_bytes, staged.d2h_bytes
 
     ms, h2d, d2h = measure(host_out=True)
-    ms_dev, _, _ = measure(host_out=False)
+    ms_dev, h2d_dev, _ = measure(host_out=False)
     return {"value": world * B * steps / (ms / 1000.0), "unit": UNIT, "h2d_bytes_per_step": int(h2d),
             "d2h_bytes_per_step": int(d2h), "steps": steps, "ms_per_step": ms / steps,
-            "path": "SampleParams -> collate_raw_clips (pinned) -> StagedPreprocess: H2D | fused kernel | D2H of "
-                    "[slow, fast] to pinned memory, 3 slots",
+            "path": "SampleParams -> collate_raw_clips (pinned) -> StagedPreprocess: H2D of whole clips | fused kernel "
+                    "| D2H of [slow, fast] to pinned memory, 3 slots",
             # informational: the same pipeline when the result stays on the device for the model
             # (what a training step consumes), i.e. without the D2H leg
             "device_resident_result": {"value": world * B * steps / (ms_dev / 1000.0), "unit": UNIT,
-                                       "ms_per_step": ms_dev / steps, "d2h_bytes_per_step": 0}}
+                                       "ms_per_step": ms_dev / steps, "h2d_bytes_per_step": int(h2d_dev),
+                                       "d2h_bytes_per_step": 0,
+                                       "path": "H2D of the frames the transform selects (pva_upload_selected_frames) "
+                                               "| fused kernel"}}
 
 
 def main():
@@ -434,6 +443,8 @@ def main():
     ap.add_argument("--e2e-steps", dest="e2e_steps", type=int, default=40)
     ap.add_argument("--cpu-seconds", dest="cpu_seconds", type=float, default=12.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--upload-all-frames", action="store_true",
+                    help="e2e: copy whole clips to the device instead of only the frames the transform selects")
     ap.add_argument("--batch", type=int, default=0, help="override the workload's batch (experiments)")
     ap.add_argument("--size", type=int, default=0, help="fix the short-side scale (bandwidth sweep)")
     ap.add_argument("--graph", dest="graph", action="store_true", default=True,

@@ -148,6 +148,22 @@ int pva_build_norm_lut(const float* mean, const float* std, int32_t channels, fl
 int pva_source_footprint(int32_t h, int32_t w, int32_t oh, int32_t ow, int32_t top, int32_t left,
                          int32_t crop, int32_t* fh, int32_t* fw);
 
+/*
+ * Host -> device copy of only the frames UniformTemporalSubsample (run.py:82) would select,
+ * for one clip: the frame gather is folded into the DMA addressing, so half of a 64-frame clip
+ * never crosses PCIe.  Replaces the device placement of the batch (run.py:196-198) for callers
+ * that keep decoded clips in pinned host memory.
+ *
+ *   host_src  : HOST (pinned, for the copy to be asynchronous), uint8 [channels][t_in][h][w]
+ *   dev_dst   : DEVICE, uint8 [channels][n_frames][h][w]; preprocess it with t_in = n_frames and
+ *               frame_idx = 0, 1, ..., n_frames - 1
+ *   frame_idx : HOST, n_frames indices into [0, t_in)
+ * Issues one cudaMemcpy2DAsync per run of equally spaced indices and channel on `stream`;
+ * allocates nothing.
+ */
+int pva_upload_selected_frames(const void* host_src, void* dev_dst, int32_t channels, int32_t t_in, int32_t h,
+                               int32_t w, const int32_t* frame_idx, int32_t n_frames, void* stream);
+
 int pva_last_launch_info(PvaLaunchInfo* info);
 
 /* (major << 16) | minor */

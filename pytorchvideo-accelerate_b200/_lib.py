@@ -29,6 +29,7 @@ EXPORTED_SYMBOLS = (
     "pva_preprocess",
     "pva_build_norm_lut",
     "pva_source_footprint",
+    "pva_upload_selected_frames",
     "pva_last_launch_info",
     "pva_version",
     "pva_last_error_string",
@@ -119,6 +120,9 @@ def load_library() -> ctypes.CDLL:
     lib.pva_build_norm_lut.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int32, ctypes.c_void_p]
     lib.pva_source_footprint.restype = ctypes.c_int
     lib.pva_source_footprint.argtypes = [ctypes.c_int32] * 7 + [ctypes.POINTER(ctypes.c_int32)] * 2
+    lib.pva_upload_selected_frames.restype = ctypes.c_int
+    lib.pva_upload_selected_frames.argtypes = [ctypes.c_void_p, ctypes.c_void_p] + [ctypes.c_int32] * 4 + [
+        ctypes.POINTER(ctypes.c_int32), ctypes.c_int32, ctypes.c_void_p]
     lib.pva_last_launch_info.restype = ctypes.c_int
     lib.pva_last_launch_info.argtypes = [ctypes.POINTER(PvaLaunchInfo)]
     lib.pva_version.restype = ctypes.c_int32

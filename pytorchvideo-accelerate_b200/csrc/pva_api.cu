@@ -86,6 +86,43 @@ int pva_source_footprint(int32_t h, int32_t w, int32_t oh, int32_t ow, int32_t t
     return PVA_OK;
 }
 
+int pva_upload_selected_frames(const void* host_src, void* dev_dst, int32_t channels, int32_t t_in, int32_t h,
+                               int32_t w, const int32_t* frame_idx, int32_t n_frames, void* stream_v) {
+    if (!host_src || !dev_dst || !frame_idx)
+        return fail(PVA_ERR_INVALID_ARGUMENT, "pva_upload_selected_frames: NULL argument");
+    if (channels < 1 || t_in < 1 || h < 1 || w < 1 || n_frames < 1)
+        return fail(PVA_ERR_INVALID_ARGUMENT, "pva_upload_selected_frames: empty shape");
+    for (int j = 0; j < n_frames; ++j)
+        if (frame_idx[j] < 0 || frame_idx[j] >= t_in)
+            return fail(PVA_ERR_INVALID_ARGUMENT, "frame_idx[%d]=%d outside [0, %d)", j, frame_idx[j], t_in);
+    cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_v);
+    const size_t plane = (size_t)h * w;
+    const unsigned char* src = static_cast<const unsigned char*>(host_src);
+    unsigned char* dst = static_cast<unsigned char*>(dev_dst);
+    for (int c = 0; c < channels; ++c) {
+        int j = 0;
+        while (j < n_frames) {
+            // longest run j, j+1, ... whose source frames are equally spaced (forward)
+            int len = 1;
+            if (j + 1 < n_frames && frame_idx[j + 1] > frame_idx[j]) {
+                const int step = frame_idx[j + 1] - frame_idx[j];
+                len = 2;
+                while (j + len < n_frames && frame_idx[j + len] - frame_idx[j + len - 1] == step) ++len;
+            }
+            const size_t spitch = len > 1 ? (size_t)(frame_idx[j + 1] - frame_idx[j]) * plane : plane;
+            cudaError_t ce = cudaMemcpy2DAsync(dst + ((size_t)c * n_frames + j) * plane, plane,
+                                               src + ((size_t)c * t_in + frame_idx[j]) * plane, spitch, plane,
+                                               (size_t)len, cudaMemcpyHostToDevice, stream);
+            if (ce != cudaSuccess) {
+                (void)cudaGetLastError();
+                return fail(PVA_ERR_CUDA, "cudaMemcpy2DAsync failed: %s", cudaGetErrorString(ce));
+            }
+            j += len;
+        }
+    }
+    return PVA_OK;
+}
+
 int pva_preprocess(const PvaClipDesc* clips, int32_t n_clips, const PvaPlan* plan, void* fast_out, void* slow_out,
                    void* stream_v) {
     using namespace pva;

@@ -16,14 +16,19 @@ from typing import List, Optional, Sequence
 
 import torch
 
-from .geometry import ClipParams
+import ctypes
+
+from . import _lib
+from .geometry import ClipParams, temporal_indices
 from .transforms import GpuClipTransform
 
 
 class _Slot:
     def __init__(self, t: GpuClipTransform, batch: int, clip_shape: Sequence[int], device: torch.device,
-                 host_out: bool):
-        self.dev_in = torch.empty((batch,) + tuple(clip_shape), dtype=torch.uint8, device=device)
+                 host_out: bool, selected_frames: bool):
+        c, t_in, h, w = clip_shape
+        frames = t.num_frames if selected_frames else t_in
+        self.dev_in = torch.empty((batch, c, frames, h, w), dtype=torch.uint8, device=device)
         self.raw_out = t.alloc_outputs(batch, device)
         self.host_out = [torch.empty(r.shape, dtype=r.dtype, pin_memory=True) for r in self.raw_out] if host_out else None
         self.in_ready = torch.cuda.Event()
@@ -35,10 +40,16 @@ class _Slot:
 class StagedPreprocess:
     """``submit(host_clips, params)`` enqueues H2D + kernel (+ D2H) for one batch and returns a
     ticket; ``result(ticket)`` waits for that batch only.  ``host_clips`` must be a pinned
-    ``B x C x T x H x W`` uint8 tensor of the shape given at construction."""
+    ``B x C x T x H x W`` uint8 tensor of the shape given at construction.
+
+    With ``upload_selected_frames=True`` only the frames ``UniformTemporalSubsample`` selects
+    (``run.py:82``) are copied to the device -- ``pva_upload_selected_frames`` folds the gather
+    into strided DMA copies -- which halves the PCIe traffic of the usual 64 -> 32 frame case; the
+    kernel then reads every frame of the compact device clip."""
 
     def __init__(self, transform: GpuClipTransform, batch: int, clip_shape: Sequence[int],
-                 device: Optional[torch.device] = None, depth: int = 3, host_out: bool = False):
+                 device: Optional[torch.device] = None, depth: int = 3, host_out: bool = False,
+                 upload_selected_frames: bool = False):
         if depth < 2:
             raise ValueError("depth must be at least 2 to overlap anything")
         self.t = transform
@@ -46,12 +57,16 @@ class StagedPreprocess:
         self.batch = batch
         self.clip_shape = tuple(clip_shape)
         self.host_out = host_out
-        self.slots = [_Slot(transform, batch, clip_shape, self.device, host_out) for _ in range(depth)]
+        self.selected = bool(upload_selected_frames)
+        self.slots = [_Slot(transform, batch, clip_shape, self.device, host_out, self.selected) for _ in range(depth)]
+        idx = temporal_indices(self.clip_shape[1], transform.num_frames)
+        self._idx = (ctypes.c_int32 * len(idx))(*idx)
+        self._lib = _lib.load_library()
         self.s_in = torch.cuda.Stream(self.device)
         self.s_run = torch.cuda.Stream(self.device)
         self.s_out = torch.cuda.Stream(self.device)
         self._n = 0
-        self.h2d_bytes = self.slots[0].dev_in.numel()
+        self.h2d_bytes = self.slots[0].dev_in.numel()  # bytes that actually cross PCIe per batch
         self.d2h_bytes = sum(r.numel() * r.element_size() for r in self.slots[0].raw_out) if host_out else 0
 
     def submit(self, host_clips: torch.Tensor, params: Sequence[ClipParams]) -> int:
@@ -61,7 +76,19 @@ class StagedPreprocess:
         with torch.cuda.stream(self.s_in):
             if slot.used:
                 self.s_in.wait_event(slot.kernel_done)  # the kernel that read this slot has finished
-            slot.dev_in.copy_(host_clips, non_blocking=True)
+            if self.selected:
+                if not host_clips.is_contiguous():
+                    raise ValueError("upload_selected_frames needs a contiguous host batch")
+                c, t_in, h, w = self.clip_shape
+                n = self.t.num_frames
+                src, dst = host_clips.data_ptr(), slot.dev_in.data_ptr()
+                with torch.cuda.device(self.device):
+                    for b in range(self.batch):
+                        rc = self._lib.pva_upload_selected_frames(src + b * c * t_in * h * w, dst + b * c * n * h * w,
+                                                                  c, t_in, h, w, self._idx, n, self.s_in.cuda_stream)
+                        _lib.raise_for_status(rc)
+            else:
+                slot.dev_in.copy_(host_clips, non_blocking=True)
             slot.in_ready.record(self.s_in)
         with torch.cuda.stream(self.s_run):
             self.s_run.wait_event(slot.in_ready)

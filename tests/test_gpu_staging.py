@@ -9,12 +9,35 @@ from _util import synth_clip
 pytestmark = pytest.mark.gpu
 
 
+def test_upload_selected_frames_is_the_temporal_gather(cuda_device):
+    """The strided DMA upload lands exactly index_select(clip, 1, linspace(0, T-1, n).long())."""
+    import ctypes
+
+    from pva_b200 import _lib
+
+    lib = _lib.load_library()
+    for t_in, n in [(64, 32), (80, 16), (16, 16), (5, 8), (33, 7)]:
+        clip = synth_clip((3, t_in, 40, 52), t_in * 100 + n).pin_memory()
+        idx = pva_b200.temporal_indices(t_in, n)
+        dst = torch.zeros((3, n, 40, 52), dtype=torch.uint8, device=cuda_device)
+        arr = (ctypes.c_int32 * n)(*idx)
+        rc = lib.pva_upload_selected_frames(clip.data_ptr(), dst.data_ptr(), 3, t_in, 40, 52, arr, n,
+                                            torch.cuda.current_stream().cuda_stream)
+        assert rc == 0, _lib.last_error()
+        torch.cuda.synchronize()
+        assert torch.equal(dst.cpu(), clip.index_select(1, torch.tensor(idx)))
+    arr = (ctypes.c_int32 * 2)(0, 9)
+    assert lib.pva_upload_selected_frames(clip.data_ptr(), dst.data_ptr(), 3, 5, 40, 52, arr, 2, None) == -1
+
+
+@pytest.mark.parametrize("selected", [False, True])
 @pytest.mark.parametrize("host_out", [False, True])
-def test_staged_pipeline_matches_direct_calls(host_out, cuda_device):
+def test_staged_pipeline_matches_direct_calls(host_out, selected, cuda_device):
     kw = dict(min_short_side_scale=128, max_short_side_scale=160, crop_size=128, num_frames=8, training=True)
     t = pva_b200.make_transform(**kw)
     shape = (3, 16, 128, 172)
-    staged = pva_b200.StagedPreprocess(t, 4, shape, cuda_device, depth=2, host_out=host_out)
+    staged = pva_b200.StagedPreprocess(t, 4, shape, cuda_device, depth=2, host_out=host_out,
+                                       upload_selected_frames=selected)
     torch.manual_seed(3)
     batches = []
     for b in range(5):  # more batches than slots: slots are reused
