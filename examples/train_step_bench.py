@@ -93,7 +93,7 @@ def main():
         loader = torch.utils.data.DataLoader(ds, batch_size=args.batch, num_workers=workers, pin_memory=True,
                                              collate_fn=pva_b200.collate_raw_clips, persistent_workers=True,
                                              prefetch_factor=4)
-        to_device = pva_b200.GpuPreprocess(t, dev)
+        to_device = pva_b200.GpuPreprocess(t, dev, upload_selected_frames=True)
     elif args.feed == "cpu":
         from oracle import pipeline  # the reference's CPU transform (restated); baseline arm only
 

@@ -64,3 +64,17 @@ def check(staged, t, ticket, batch, host_out):
         if host_out:
             g = g.permute(0, 4, 1, 2, 3)  # raw N x T x S x S x C -> logical
         assert torch.equal(g.cpu(), w.cpu())
+
+
+def test_gpu_preprocess_with_selected_frame_upload(cuda_device):
+    kw = dict(min_short_side_scale=128, max_short_side_scale=160, crop_size=128, num_frames=8, training=True)
+    t = pva_b200.make_transform(**kw)
+    sp = pva_b200.SampleParams(t)
+    torch.manual_seed(4)
+    samples = [sp({"video": synth_clip((3, 16, 128, 170), 60 + i), "label": i}) for i in range(3)]
+    batch = pva_b200.collate_raw_clips(samples)
+    batch["video"] = batch["video"].pin_memory()
+    a = pva_b200.GpuPreprocess(t, cuda_device, upload_selected_frames=True)(dict(batch))["video"]
+    b = pva_b200.GpuPreprocess(t, cuda_device)(dict(batch))["video"]
+    torch.cuda.synchronize()
+    assert all(torch.equal(x, y) for x, y in zip(a, b))
