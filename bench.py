@@ -57,16 +57,23 @@ WORKLOADS = {
 # --------------------------------------------------------------------------------------
 # CPU arm (oracle port of the reference transform), duration-bounded, one process per core
 # --------------------------------------------------------------------------------------
+def reference_cpu_transform(**kwargs):
+    """The reference's CPU transform (oracle restatement of run.py:68-102) for the CPU-baseline legs.
+    bench.py's cpu_baseline / reference arm is the one place outside tests/ and smoke() that may
+    execute oracle/; examples/train_step_bench.py's CPU feeder goes through here as well."""
+    from oracle import pipeline
+
+    return pipeline.make_transform(**kwargs)
+
+
 def _cpu_worker(widx, shape, kwargs, counter, go, stop):
     import torch
-
-    from oracle import pipeline  # bench.py's cpu_baseline / reference arm may execute oracle/
 
     torch.set_num_threads(1)  # what a DataLoader worker gets (torch/utils/data/_utils/worker.py)
     torch.manual_seed(42 + widx)
     g = torch.Generator().manual_seed(1234 + widx)
     clip = torch.randint(0, 256, shape, dtype=torch.uint8, generator=g)
-    transform = pipeline.make_transform(**kwargs)
+    transform = reference_cpu_transform(**kwargs)
     transform({"video": clip})  # warm the allocator
     go.wait()
     while not stop.is_set():

@@ -95,9 +95,9 @@ def main():
                                              prefetch_factor=4)
         to_device = pva_b200.GpuPreprocess(t, dev, upload_selected_frames=True)
     elif args.feed == "cpu":
-        from oracle import pipeline  # the reference's CPU transform (restated); baseline arm only
+        from bench import reference_cpu_transform  # bench.py's CPU-baseline leg: the reference's transform
 
-        ds = SyntheticClips(n_items, pipeline.make_transform(**kw))
+        ds = SyntheticClips(n_items, reference_cpu_transform(**kw))
         loader = torch.utils.data.DataLoader(ds, batch_size=args.batch, num_workers=workers, pin_memory=True,
                                              persistent_workers=True, prefetch_factor=2)
     else:
