@@ -774,8 +774,15 @@ cudaError_t launch_t(const TiledArgs& a, int norm, bool fastx, int grid, int sme
 #define PVA_TILED_CASE(N, F)                                                                          \
     if (norm == N && fastx == F) {                                                                    \
         auto kern = pva_tiled_kernel<OutT, N, F>;                                                     \
-        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem); \
-        if (e != cudaSuccess) return e;                                                               \
+        /* the opt-in shared-memory ceiling only ever needs raising (per device, per variant) */     \
+        static int configured[64] = {};                                                               \
+        int dev = 0;                                                                                  \
+        cudaGetDevice(&dev);                                                                          \
+        if (dev < 0 || dev >= 64 || configured[dev] < smem) {                                         \
+            cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem); \
+            if (e != cudaSuccess) return e;                                                           \
+            if (dev >= 0 && dev < 64) configured[dev] = smem;                                         \
+        }                                                                                             \
         cudaLaunchConfig_t cfg = {};                                                                  \
         cfg.gridDim = dim3(grid);                                                                     \
         cfg.blockDim = dim3(kBlockThreads);                                                           \

@@ -120,6 +120,9 @@ class GpuClipTransform:
         self.n_slow = self.num_frames // self.slowfast_alpha if self.is_slowfast else 0
         self._slow_tab = _IdxTable(pack_indices(self.num_frames, self.slowfast_alpha) if self.is_slowfast else ())
         self._idx_cache: Dict[int, _IdxTable] = {}
+        # the reference converts mean/std to fp32 tensors (torchvision normalize): round once, here
+        self._mean32 = [float(torch.tensor(m, dtype=torch.float32)) for m in self.mean]
+        self._std32 = [float(torch.tensor(v, dtype=torch.float32)) for v in self.std]
         self._lib = _lib.load_library()  # loud failure here, not at first use
 
     # ---- host-side draws -------------------------------------------------------------
@@ -148,10 +151,9 @@ class GpuClipTransform:
         plan.n_slow = self.n_slow
         plan.crop = self.crop_size
         plan.slow_idx = self._slow_tab.ptr if self.n_slow else None
-        # the reference converts mean/std to fp32 tensors (torchvision normalize)
-        for c, (m, s) in enumerate(zip(self.mean, self.std)):
-            plan.mean[c] = float(torch.tensor(m, dtype=torch.float32))
-            plan.std[c] = float(torch.tensor(s, dtype=torch.float32))
+        for c, (m, s) in enumerate(zip(self._mean32, self._std32)):
+            plan.mean[c] = m
+            plan.std[c] = s
         plan.out_dtype = _DTYPES[self.out_dtype]
         plan.out_layout = _lib.PVA_LAYOUT_THWC if self.channels_last else _lib.PVA_LAYOUT_CTHW
         plan.norm_mode = _NORM[self.norm_mode]
