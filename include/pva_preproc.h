@@ -34,7 +34,7 @@ typedef enum PvaStatus {
     PVA_ERR_INVALID_ARGUMENT = -1, /* NULL pointer, non-positive size, bad enum                       */
     PVA_ERR_CROP_TOO_LARGE = -2,   /* crop window does not fit the resized frame: the reference raises
                                       ValueError (torchvision transforms.py:647-648); no zero padding  */
-    PVA_ERR_UNSUPPORTED = -3,      /* shape outside what the kernels implement (see pva_limits)       */
+    PVA_ERR_UNSUPPORTED = -3,      /* shape outside the limits listed below                           */
     PVA_ERR_CUDA = -4              /* a CUDA runtime call failed; text holds cudaGetErrorString       */
 } PvaStatus;
 
@@ -62,6 +62,10 @@ typedef enum PvaKernel { PVA_KERNEL_AUTO = 0, PVA_KERNEL_GENERIC = 1, PVA_KERNEL
 typedef enum PvaSrcType { PVA_SRC_U8 = 0, PVA_SRC_F32 = 1 } PvaSrcType;
 
 #define PVA_MAX_CHANNELS 4
+/* Limits: 1..4 channels; n_fast, n_slow <= 128; t_in <= 65535; any h, w, crop.  More than 128 clips
+ * or 8 distinct frame_idx tables per call are handled with several launches.  The tiled kernel takes
+ * 3-channel uint8 clips, the channels-last layout and crops up to 2048; everything else runs on the
+ * generic kernel (PVA_KERNEL_AUTO decides; PVA_KERNEL_TILED returns PVA_ERR_UNSUPPORTED instead). */
 
 /*
  * One clip and its per-clip draws.  Replaces the arguments the reference passes implicitly
