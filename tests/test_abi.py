@@ -115,3 +115,12 @@ def test_host_helpers():
                  (97, 131, 77, 103, 3, 11, 64)]:
         assert _lib.source_footprint(*args) == c_oracle.footprint(*args)
     assert _lib.source_footprint(256, 340, 256, 340, 0, 42, 256) == (256, 257)
+
+
+def test_upload_helper_validates_without_a_gpu():
+    lib = _lib.load_library()
+    idx = (ctypes.c_int32 * 2)(0, 5)
+    assert lib.pva_upload_selected_frames(None, 0x2000, 3, 4, 8, 8, idx, 2, None) == _lib.PVA_ERR_INVALID_ARGUMENT
+    assert lib.pva_upload_selected_frames(0x1000, 0x2000, 3, 4, 8, 8, idx, 2, None) == _lib.PVA_ERR_INVALID_ARGUMENT
+    assert "frame_idx[1]=5" in _lib.last_error()
+    assert lib.pva_upload_selected_frames(0x1000, 0x2000, 0, 4, 8, 8, idx, 2, None) == _lib.PVA_ERR_INVALID_ARGUMENT
