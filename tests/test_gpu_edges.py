@@ -120,3 +120,18 @@ def test_extreme_windows_at_the_frame_corners(cuda_device):
                 rs, rf = oracle_clip(clip, p, kw)
                 assert np.array_equal(fast.cpu().numpy(), rf), (size, top, left, flip)
                 assert np.array_equal(slow.cpu().numpy(), rs)
+
+
+@pytest.mark.parametrize("kernel", ["generic", "tiled"])
+def test_maximum_frame_counts(kernel, cuda_device):
+    """n_fast = 128 (the ABI's limit) out of a 300-frame clip, alpha = 1 so that n_slow = 128 as well."""
+    kw = full_kwargs(dict(min_short_side_scale=32, crop_size=32, num_frames=128, slowfast_alpha=1))
+    clip = synth_clip((3, 300, 36, 48), 4242)
+    t = pva_b200.make_transform(**kw, out_dtype=torch.float32, norm_mode="exact", kernel=kernel)
+    p = t.sample_params(36, 48)
+    slow, fast = t.explicit(clip.cuda(), p)
+    assert fast.shape == (3, 128, 32, 32) and slow.shape == (3, 128, 32, 32)
+    rs, rf = oracle_clip(clip, p, kw)
+    assert np.array_equal(fast.cpu().numpy(), rf) and np.array_equal(slow.cpu().numpy(), rs)
+    with pytest.raises(NotImplementedError, match="n_fast"):
+        pva_b200.make_transform(**dict(kw, num_frames=129), kernel=kernel).explicit(clip.cuda(), p)
