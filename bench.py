@@ -272,7 +272,7 @@ def run_b200_arm(args):
     for s in range(n_sets):
         clips = torch.randint(0, 256, (B,) + tuple(shape), dtype=torch.uint8, generator=gen).to(dev)
         params = [t.sample_params(shape[2], shape[3]) for _ in range(B)]
-        sets.append(t.prepare_batch(clips, params))
+        sets.append(t.prepare_batch(clips, params, clips_ready=True))  # resident and complete before the timed region
         b = 0
         for p in params:
             fh, fw = _lib.source_footprint(shape[2], shape[3], p.oh, p.ow, p.top, p.left, crop)
@@ -497,9 +497,11 @@ def main():
                     help="e2e: copy whole clips to the device instead of only the frames the transform selects")
     ap.add_argument("--batch", type=int, default=0, help="override the workload's batch (experiments)")
     ap.add_argument("--size", type=int, default=0, help="fix the short-side scale (bandwidth sweep)")
-    ap.add_argument("--graph", dest="graph", action="store_true", default=True,
-                    help="replay the steps from a captured CUDA graph (default)")
-    ap.add_argument("--no-graph", dest="graph", action="store_false", help="plain launches through the C ABI")
+    ap.add_argument("--graph", dest="graph", action="store_true", default=False,
+                    help="replay the steps from a captured CUDA graph (4 launches per replay)")
+    ap.add_argument("--no-graph", dest="graph", action="store_false",
+                    help="plain launches through the C ABI (default: every launch is chained to the previous "
+                         "one by programmatic dependent launch; a graph replay boundary is a full barrier)")
     args = ap.parse_args()
     if args.warmup < 3:
         args.warmup = 3  # timing rule: at least 3 warm-up steps

@@ -62,6 +62,16 @@ typedef enum PvaKernel { PVA_KERNEL_AUTO = 0, PVA_KERNEL_GENERIC = 1, PVA_KERNEL
 typedef enum PvaSrcType { PVA_SRC_U8 = 0, PVA_SRC_F32 = 1 } PvaSrcType;
 
 #define PVA_MAX_CHANNELS 4
+
+/* PvaPlan.flags.
+ * PVA_FLAG_CLIPS_READY: the caller asserts that the clip bytes were complete before the previous
+ * KERNEL of this stream was launched -- they came from a copy, or from a kernel further back --
+ * and that no clip aliases the outputs of the previous pva_preprocess call.  Consecutive calls
+ * on one stream then overlap: the next launch reads clips and computes while the previous one is
+ * still draining, and waits for it only before its first store (output buffers may be reused
+ * freely; that ordering is always kept).  Without the flag a launch waits for the previous
+ * kernel before it touches memory at all. */
+#define PVA_FLAG_CLIPS_READY 1
 /* Limits: 1..4 channels; n_fast, n_slow <= 128; t_in <= 65535; any h, w, crop.  More than 128 clips
  * or 8 distinct frame_idx tables per call are handled with several launches.  The tiled kernel takes
  * 3-channel uint8 clips, the channels-last layout and crops up to 2048; everything else runs on the
@@ -114,7 +124,8 @@ typedef struct PvaPlan {
     int32_t norm_mode;  /* PvaNormMode */
     int32_t kernel;     /* PvaKernel  */
     int32_t src_type;   /* PvaSrcType */
-    int32_t reserved[3];
+    int32_t flags;      /* PVA_FLAG_* */
+    int32_t reserved[2];
 } PvaPlan;
 
 /* What the last pva_preprocess call of this thread launched (for tests and bench.py). */

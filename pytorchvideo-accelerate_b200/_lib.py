@@ -24,6 +24,7 @@ PVA_LAYOUT_CTHW, PVA_LAYOUT_THWC = 0, 1
 PVA_NORM_EXACT, PVA_NORM_AFFINE = 0, 1
 PVA_KERNEL_AUTO, PVA_KERNEL_GENERIC, PVA_KERNEL_TILED = 0, 1, 2
 PVA_SRC_U8, PVA_SRC_F32 = 0, 1
+PVA_FLAG_CLIPS_READY = 1
 
 EXPORTED_SYMBOLS = (
     "pva_preprocess",
@@ -69,7 +70,8 @@ class PvaPlan(ctypes.Structure):
         ("norm_mode", ctypes.c_int32),
         ("kernel", ctypes.c_int32),
         ("src_type", ctypes.c_int32),
-        ("reserved", ctypes.c_int32 * 3),
+        ("flags", ctypes.c_int32),
+        ("reserved", ctypes.c_int32 * 2),
     ]
 
 

@@ -187,6 +187,7 @@ int pva_preprocess(const PvaClipDesc* clips, int32_t n_clips, const PvaPlan* pla
     kp.n_slow = plan->n_slow;
     kp.crop = crop;
     kp.src_f32 = plan->src_type == PVA_SRC_F32 ? 1 : 0;
+    kp.clips_ready = (plan->flags & PVA_FLAG_CLIPS_READY) ? 1 : 0;
     kp.fast_clip_elems = (long long)C * plan->n_fast * crop * crop;
     kp.slow_clip_elems = (long long)C * plan->n_slow * crop * crop;
     for (int j = 0; j < plan->n_slow; ++j) kp.slow_idx[j] = (uint16_t)plan->slow_idx[j];

@@ -34,6 +34,7 @@ struct KParams {
     void* slow_out;  // nullptr for a single pathway
     int n_clips, C, n_fast, n_slow, crop;
     int src_f32;        // source clips are float32 (0..255 valued) instead of uint8: generic kernel only
+    int clips_ready;    // PVA_FLAG_CLIPS_READY: reading the clips need not wait for the previous kernel
     long long fast_clip_elems;  // C * n_fast * crop * crop
     long long slow_clip_elems;
     float na[kMaxChannels];  // AFFINE: out = fma(p, na, nb), p = bilinear over raw bytes

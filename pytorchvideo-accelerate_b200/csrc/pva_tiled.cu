@@ -70,7 +70,7 @@ struct TileGeom {
     int bulk_store;    // 1: cp.async.bulk stores are legal (alignment), 0: plain stores
     int total_tiles;
     int off_ytab, off_in, off_out, off_lut;
-    int pdl;         // launched with programmatic stream serialization
+    int pdl;         // programmatic dependent launch: 0 off, 1 wait before the first store, 2 wait at the start
     int load_rows;   // 1: column-cropped source rows through 128-bit cp.async, one row per producer lane;
                      // 0: one cp.async.bulk per plane over the full-width row band
     int l2hint;      // bit 0: loads evict_first, bit 1: stores evict_first
@@ -270,10 +270,14 @@ __global__ void __launch_bounds__(kBlockThreads, 1) pva_tiled_kernel(const __gri
     }
     __syncthreads();
     if (tg.pdl) {
-        // Programmatic dependent launch: everything above ran while the previous kernel of the
-        // stream was still finishing; from here on global memory is touched, so wait for it.
+        // Programmatic dependent launch.  This CTA may run while the previous kernel of the stream
+        // is still finishing (it starts on an SM that kernel has already left).  Reading the clips
+        // and computing is safe then -- the only kernel that signals its dependents early is this
+        // one, and it never writes clip bytes -- but nothing may be WRITTEN before the previous
+        // kernel has completed (the caller may be reusing the output buffers): the threads that
+        // issue stores wait right before their first store, everybody else never has to.
         asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
-        asm volatile("griddepcontrol.wait;" ::: "memory");
+        if (!tg.bulk_store || tg.pdl == 2) asm volatile("griddepcontrol.wait;" ::: "memory");
     }
 
     const uint32_t in_base = smem_u32(smem + tg.off_in);
@@ -389,6 +393,7 @@ __global__ void __launch_bounds__(kBlockThreads, 1) pva_tiled_kernel(const __gri
     for (int i = 0; i < kPx; ++i) off0[i] = off1[i] = 0, lx0[i] = lx1[i] = 0.f;
 
     int strip_it = 0;  // staging buffer index of this strip
+    bool may_store = !(tg.pdl == 1 && tg.bulk_store);  // false until griddepcontrol.wait has been executed
 
     for (int t = t_begin + group; t < t_end; t += tg.groups) {
         const int it = t - t_begin;
@@ -595,6 +600,10 @@ __global__ void __launch_bounds__(kBlockThreads, 1) pva_tiled_kernel(const __gri
                 }
                 named_bar(bar_strip, strip_threads);
                 if (g_col == 0 && rows > 0 && !(tg.debug & 1)) {
+                    if (!may_store) {
+                        asm volatile("griddepcontrol.wait;" ::: "memory");
+                        may_store = true;
+                    }
                     const uint32_t ssrc = smem_u32(stage_out);
                     const uint32_t bytes = (uint32_t)((size_t)rows * crop * 3 * esz);
                     if (tg.l2hint & 2) {
@@ -824,7 +833,9 @@ cudaError_t launch_tiled(KParams& p, int out_dtype, int layout, int norm, cudaSt
         fastx = fastx && (g.w <= g.ow) && (g.w % 4 == 0) && ((uintptr_t)g.src % 4 == 0);
     }
     a.p = p;
-    a.g.pdl = env_int("PVA_TILED_PDL", 1);
+    // 1: wait for the previous kernel only before the first store (PVA_FLAG_CLIPS_READY); 2: wait
+    // before touching memory at all; 0: no programmatic dependent launch
+    a.g.pdl = env_int("PVA_TILED_PDL", p.clips_ready ? 1 : 2);
     a.g.l2hint = env_int("PVA_TILED_L2HINT", 3);  // clip bytes are read once, outputs are consumed later: stream both
     int dev = 0, sms = 148;
     cudaGetDevice(&dev);

@@ -94,7 +94,9 @@ class StagedPreprocess:
             self.s_run.wait_event(slot.in_ready)
             if slot.used and self.host_out:
                 self.s_run.wait_event(slot.out_ready)  # the previous result has left the slot
-            prepared = self.t.prepare_batch(slot.dev_in, params, out=slot.raw_out)
+            # the clips arrived through a copy on another stream (event-ordered): nothing the previous
+            # kernel on s_run did can have produced them
+            prepared = self.t.prepare_batch(slot.dev_in, params, out=slot.raw_out, clips_ready=True)
             prepared.launch_raw(self.s_run.cuda_stream)
             slot.kernel_done.record(self.s_run)
         if self.host_out:

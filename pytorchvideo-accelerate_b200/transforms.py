@@ -144,8 +144,9 @@ class GpuClipTransform:
             tab = self._idx_cache[t_in] = _IdxTable(temporal_indices(t_in, self.num_frames))
         return tab
 
-    def _plan(self, src_dtype: torch.dtype = torch.uint8) -> _lib.PvaPlan:
+    def _plan(self, src_dtype: torch.dtype = torch.uint8, clips_ready: bool = False) -> _lib.PvaPlan:
         plan = _lib.PvaPlan()
+        plan.flags = _lib.PVA_FLAG_CLIPS_READY if clips_ready else 0
         plan.channels = len(self.mean)
         plan.n_fast = self.num_frames
         plan.n_slow = self.n_slow
@@ -185,11 +186,16 @@ class GpuClipTransform:
         return t.permute(0, 4, 1, 2, 3) if self.channels_last else t
 
     def prepare_batch(self, clips: Union[torch.Tensor, Sequence[torch.Tensor]], params: Sequence[ClipParams],
-                      out: Optional[Sequence[torch.Tensor]] = None) -> "PreparedBatch":
+                      out: Optional[Sequence[torch.Tensor]] = None, clips_ready: bool = False) -> "PreparedBatch":
         """Validate a batch and build its descriptor table once; ``.launch()`` then costs a
         single C call.  ``clips``: a ``B x C x T x H x W`` uint8 cuda tensor or a sequence of
         ``C x T x H x W`` uint8 cuda tensors (ragged shapes allowed).  ``out`` may supply raw
         output buffers from :meth:`alloc_outputs`.
+
+        ``clips_ready=True`` sets ``PVA_FLAG_CLIPS_READY`` (``include/pva_preproc.h``): say so when
+        the clip bytes were complete before the previous kernel on the launch stream started (they
+        came from a copy, or have been resident for a while) -- consecutive launches then overlap.
+        Leave it off when a kernel enqueued right before this call produces the clips.
         """
         clip_list = list(clips.unbind(0)) if isinstance(clips, torch.Tensor) and clips.dim() == 5 else list(clips)
         n = len(clip_list)
@@ -222,7 +228,7 @@ class GpuClipTransform:
             d.oh, d.ow, d.top, d.left, d.flip = p.oh, p.ow, p.top, p.left, int(p.flip)
         if out is None:
             out = self.alloc_outputs(n, device)
-        return PreparedBatch(self, descs, n, keep, list(out), device, clip_list[0].dtype)
+        return PreparedBatch(self, descs, n, keep, list(out), device, clip_list[0].dtype, clips_ready)
 
     def run_batch(self, clips: Union[torch.Tensor, Sequence[torch.Tensor]], params: Sequence[ClipParams],
                   out: Optional[Sequence[torch.Tensor]] = None,
@@ -270,14 +276,15 @@ class PreparedBatch:
     """A validated batch: descriptor table, plan and output buffers, ready to (re)launch."""
 
     def __init__(self, transform: GpuClipTransform, descs, n: int, clips: List[torch.Tensor],
-                 out: List[torch.Tensor], device: torch.device, src_dtype: torch.dtype = torch.uint8):
+                 out: List[torch.Tensor], device: torch.device, src_dtype: torch.dtype = torch.uint8,
+                 clips_ready: bool = False):
         self.t = transform
         self.descs = descs
         self.n = n
         self.clips = clips
         self.raw_out = out
         self.device = device
-        self.plan = transform._plan(src_dtype)
+        self.plan = transform._plan(src_dtype, clips_ready)
         self._plan_ref = ctypes.byref(self.plan)
         self.slow_raw, self.fast_raw = (out[0], out[1]) if transform.n_slow else (None, out[-1])
         self._fast_ptr = self.fast_raw.data_ptr()
@@ -415,6 +422,10 @@ class GpuPreprocess:
         video = batch["video"]
         rows = batch[PARAMS_KEY]
         params = [ClipParams.from_row(r) for r in rows.tolist()]
+        # clips that this call copies from the host are complete before any kernel it launches (a copy
+        # is not a kernel: the launch is ordered after it in full); device tensors may have just been
+        # produced by a kernel of the caller, so they get the conservative ordering
+        from_host = (not video.is_cuda) if isinstance(video, torch.Tensor) else all(not v.is_cuda for v in video)
         if (self.upload_selected_frames and isinstance(video, torch.Tensor) and not video.is_cuda
                 and video.dtype == torch.uint8 and video.is_contiguous()):
             clips = self._upload_selected(video, dev)
@@ -422,7 +433,7 @@ class GpuPreprocess:
             clips = video.to(dev, non_blocking=True)
         else:
             clips = [v.to(dev, non_blocking=True) for v in video]
-        out = self.t.run_batch(clips, params)
+        out = self.t.prepare_batch(clips, params, clips_ready=from_host).launch()
         batch["video"] = out if self.t.is_slowfast else out[0]
         del batch[PARAMS_KEY]
         return batch

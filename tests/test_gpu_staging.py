@@ -78,3 +78,28 @@ def test_gpu_preprocess_with_selected_frame_upload(cuda_device):
     b = pva_b200.GpuPreprocess(t, cuda_device)(dict(batch))["video"]
     torch.cuda.synchronize()
     assert all(torch.equal(x, y) for x, y in zip(a, b))
+
+
+def test_back_to_back_launches_into_the_same_outputs_keep_stream_order(cuda_device):
+    """PVA_FLAG_CLIPS_READY lets a launch start while the previous one drains, but it must not
+    store before that one has completed: the last launch into a reused output buffer wins."""
+    kw = dict(num_frames=32, slowfast_alpha=4, training=True)
+    t = pva_b200.make_transform(**kw)
+    torch.manual_seed(12)
+    sets = []
+    for s in range(3):
+        clips = torch.stack([synth_clip((3, 64, 256, 340), 900 + 10 * s + i) for i in range(4)]).cuda()
+        params = [t.sample_params(256, 340) for _ in range(4)]
+        sets.append((clips, params))
+    want = [[o.clone() for o in t.run_batch(c, p)] for c, p in sets]
+    shared = t.alloc_outputs(4, cuda_device)
+    prepared = [t.prepare_batch(c, p, out=shared, clips_ready=True) for c, p in sets]
+    torch.cuda.synchronize()
+    for rounds in range(20):
+        last = None
+        for i in range(7):  # no synchronisation in between: 7 launches race through one output buffer
+            last = (rounds + i) % 3
+            prepared[last].launch()
+        torch.cuda.synchronize()
+        got = prepared[last].outputs
+        assert all(torch.equal(g, w) for g, w in zip(got, want[last])), (rounds, last)
