@@ -430,11 +430,17 @@ def run_e2e(torch, pva_b200, t, wl, dev, dist, world, rank, args):
         b["params"] = [pva_b200.ClipParams.from_row(r) for r in b["pva_params"].tolist()]
         host_batches.append(b)
     def measure(host_out):
-        # Strided selected-frame upload halves the H2D bytes, but its many 2-D copies overlap worse
-        # with a concurrent full-size D2H stream than one flat copy does (3.13 vs 2.82 ms per step
-        # measured), so the host-to-host figure uploads whole clips; when the result stays on the
-        # device (no D2H leg) the selected-frame upload is what pays (1.40 vs 2.41 ms).
-        selected = (not host_out) and not args.upload_all_frames
+        # Strided selected-frame upload halves the H2D bytes.  On one GPU its many 2-D copies overlap
+        # worse with a concurrent full-size D2H stream than one flat copy does (3.13 vs 2.82 ms per
+        # step measured), so the host-to-host figure uploads whole clips there; with several ranks the
+        # host's memory system is the limit and fewer bytes win (4 GPUs: 5.13 vs 5.83 ms).  When the
+        # result stays on the device (no D2H leg) the selected-frame upload always pays (1.40 vs 2.41 ms).
+        if args.e2e_upload == "auto":
+            selected = (not host_out) or world > 1
+        else:
+            selected = args.e2e_upload == "selected"
+        if args.upload_all_frames:
+            selected = False
         staged = pva_b200.StagedPreprocess(t, B, shape, dev, depth=3, host_out=host_out,
                                            upload_selected_frames=selected)
 
@@ -468,8 +474,9 @@ def run_e2e(torch, pva_b200, t, wl, dev, dist, world, rank, args):
     ms_dev, h2d_dev, _ = measure(host_out=False)
     return {"value": world * B * steps / (ms / 1000.0), "unit": UNIT, "h2d_bytes_per_step": int(h2d),
             "d2h_bytes_per_step": int(d2h), "steps": steps, "ms_per_step": ms / steps,
-            "path": "SampleParams -> collate_raw_clips (pinned) -> StagedPreprocess: H2D of whole clips | fused kernel "
-                    "| D2H of [slow, fast] to pinned memory, 3 slots",
+            "path": "SampleParams -> collate_raw_clips (pinned) -> StagedPreprocess: H2D of "
+                    + ("whole clips" if h2d == B * int(torch.tensor(shape).prod()) else "the selected frames (strided DMA)")
+                    + " | fused kernel | D2H of [slow, fast] to pinned memory, 3 slots",
             # informational: the same pipeline when the result stays on the device for the model
             # (what a training step consumes), i.e. without the D2H leg
             "device_resident_result": {"value": world * B * steps / (ms_dev / 1000.0), "unit": UNIT,
@@ -493,6 +500,8 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--overlap-streams", dest="overlap_streams", type=int, default=2,
                     help="also time the K steps issued round-robin on this many streams (informational; 0/1 = skip)")
+    ap.add_argument("--e2e-upload", dest="e2e_upload", choices=["auto", "all", "selected"], default="auto",
+                    help="e2e H2D leg: whole clips, only the selected frames, or auto (see run_e2e)")
     ap.add_argument("--upload-all-frames", action="store_true",
                     help="e2e: copy whole clips to the device instead of only the frames the transform selects")
     ap.add_argument("--batch", type=int, default=0, help="override the workload's batch (experiments)")
