@@ -257,7 +257,7 @@ def run_b200_arm(args):
     if args.size:
         wl["kwargs"] = dict(wl["kwargs"], min_short_side_scale=args.size, max_short_side_scale=args.size)
     B, shape, kw = wl["batch"], wl["shape"], wl["kwargs"]
-    t = pva_b200.make_transform(**kw, device=dev, out_dtype=torch.float16, channels_last=True,
+    t = pva_b200.make_transform(**kw, device=dev, out_dtype=torch.float16, channels_last=not args.planar,
                                 norm_mode=args.norm_mode, kernel=args.kernel)
     esize = 2
     C, crop, n_fast, n_slow = shape[0], t.crop_size, t.num_frames, t.n_slow
@@ -388,7 +388,7 @@ def run_b200_arm(args):
         "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic",
         "config": {"workload": args.workload, "batch_per_gpu": B, "global_batch": B * world,
-                   "clip_shape": list(shape), "transform": kw, "out": "fp16 THWC (channels_last_3d)",
+                   "clip_shape": list(shape), "transform": kw, "out": "fp16 CTHW (the reference's memory order)" if args.planar else "fp16 THWC (channels_last_3d)",
                    "norm_mode": args.norm_mode, "parallelism": f"dp{world} (clips sharded per rank, no collective)",
                    "l2": f"{n_sets} rotating input/output sets = {(in_bytes + out_bytes) * n_sets >> 20} MiB > L2",
                    "launch": info, "cuda_graph": bool(args.graph)},
@@ -504,6 +504,8 @@ def main():
                     help="e2e H2D leg: whole clips, only the selected frames, or auto (see run_e2e)")
     ap.add_argument("--upload-all-frames", action="store_true",
                     help="e2e: copy whole clips to the device instead of only the frames the transform selects")
+    ap.add_argument("--planar", action="store_true",
+                    help="write the reference's contiguous C x T x S x S order instead of channels-last (experiments)")
     ap.add_argument("--batch", type=int, default=0, help="override the workload's batch (experiments)")
     ap.add_argument("--size", type=int, default=0, help="fix the short-side scale (bandwidth sweep)")
     ap.add_argument("--graph", dest="graph", action="store_true", default=False,

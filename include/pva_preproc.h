@@ -74,7 +74,7 @@ typedef enum PvaSrcType { PVA_SRC_U8 = 0, PVA_SRC_F32 = 1 } PvaSrcType;
 #define PVA_FLAG_CLIPS_READY 1
 /* Limits: 1..4 channels; n_fast, n_slow <= 128; t_in <= 65535; any h, w, crop.  More than 128 clips
  * or 8 distinct frame_idx tables per call are handled with several launches.  The tiled kernel takes
- * 3-channel uint8 clips, the channels-last layout and crops up to 2048; everything else runs on the
+ * 3-channel uint8 clips, either layout and crops up to 2048; everything else runs on the
  * generic kernel (PVA_KERNEL_AUTO decides; PVA_KERNEL_TILED returns PVA_ERR_UNSUPPORTED instead). */
 
 /*

@@ -28,8 +28,9 @@
 // The library only ever reads 16-byte granules that contain at least one byte of the clip.
 // (PVA_TILED_LOAD_ROWS=1 selects an experimental column-cropped LDGSTS load path; measured slower.)
 //
-// Layout: this kernel writes T x S x S x C (channels-last) only; the reference's C x T x S x S
-// order is served by the generic kernel.
+// Layout: T x S x S x C (channels-last, the default) or the reference's C x T x S x S.  The two differ
+// only in how a strip is staged and stored: one contiguous range of whole output rows, or three
+// ranges, one per channel plane (template parameter kPlanar).
 #include <stdlib.h>
 
 #include <type_traits>
@@ -215,6 +216,30 @@ __device__ __forceinline__ void stage_row(unsigned char* strip, int row, int cro
     }
 }
 
+// The same results for the reference's C x T x S x S order: the strip is staged as three channel
+// planes of rps x crop elements, each of which is one contiguous range of the output.
+template <typename OutT>
+__device__ __forceinline__ void stage_row_planar(unsigned char* strip, int row, int rps, int crop, int g, bool full,
+                                                 const float (&o)[kPx][3]) {
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+        OutT* base = reinterpret_cast<OutT*>(strip) + ((size_t)c * rps + row) * crop + kPx * g;
+        if (full) {
+            if (sizeof(OutT) == 4) {
+                *reinterpret_cast<float4*>(base) = make_float4(o[0][c], o[1][c], o[2][c], o[3][c]);
+            } else {
+                using P = Pack<typename std::conditional<sizeof(OutT) == 2, OutT, __half>::type>;
+                *reinterpret_cast<uint2*>(base) = make_uint2(P::two(o[0][c], o[1][c]), P::two(o[2][c], o[3][c]));
+            }
+        } else {
+            const int npx = crop - kPx * g;
+#pragma unroll
+            for (int i = 0; i < kPx; ++i)
+                if (i < npx) base[i] = to_out<OutT>(o[i][c]);
+        }
+    }
+}
+
 __device__ __forceinline__ void cp_async16(uint32_t dst, const void* src) {
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
 }
@@ -233,8 +258,9 @@ __device__ __forceinline__ __half2 bytes_as_half2(uint32_t t) {
 }
 
 // kNormT: 0 = EXACT, 1 = AFFINE with one scale for all channels (folded into the row table),
-// 2 = AFFINE with per-channel scales.
-template <typename OutT, int kNormT, bool kFastX>
+// 2 = AFFINE with per-channel scales.  kPlanar: write C x T x S x S (the reference's order) instead of
+// T x S x S x C.
+template <typename OutT, int kNormT, bool kFastX, bool kPlanar>
 __global__ void __launch_bounds__(kBlockThreads, 1) pva_tiled_kernel(const __grid_constant__ TiledArgs a) {
     extern __shared__ __align__(128) unsigned char smem[];
     constexpr int kNorm = kNormT == 0 ? kNormExact : kNormAffine;
@@ -542,7 +568,8 @@ __global__ void __launch_bounds__(kBlockThreads, 1) pva_tiled_kernel(const __gri
                         for (int i = 0; i < kPx; ++i) o[i][c] = fmaf(w0, tp[i][c], fmaf(w1, bt[i][c], b));
                     }
                 }
-                stage_row<OutT>(stage_out, y - y_begin, crop, g_col, full_group, o);
+                if (kPlanar) stage_row_planar<OutT>(stage_out, y - y_begin, tg.rps, crop, g_col, full_group, o);
+                else stage_row<OutT>(stage_out, y - y_begin, crop, g_col, full_group, o);
             };
             // One output row.  T holds source row rT (the row's upper tap), B holds rB.  When the
             // upper tap moves on to the row B already holds, the buffers swap roles (returns true)
@@ -605,6 +632,27 @@ __global__ void __launch_bounds__(kBlockThreads, 1) pva_tiled_kernel(const __gri
                         may_store = true;
                     }
                     const uint32_t ssrc = smem_u32(stage_out);
+                    if (kPlanar) {
+                        // one contiguous range per channel plane: rows x crop elements
+                        const uint32_t bytes = (uint32_t)((size_t)rows * crop * esz);
+                        const uint32_t sstep = (uint32_t)((size_t)tg.rps * crop * esz);
+                        const uint64_t pol = l2_evict_first_policy();
+#pragma unroll
+                        for (int c = 0; c < 3; ++c) {
+                            OutT* d = fast + (((size_t)c * p.n_fast + k) * crop + y_begin) * crop;
+                            if (tg.l2hint & 2) bulk_store_hint(d, ssrc + c * sstep, bytes, pol);
+                            else bulk_store(d, ssrc + c * sstep, bytes);
+                        }
+                        if (slow)
+                            for (int j = 0; j < p.n_slow; ++j)
+                                if (p.slow_idx[j] == k)
+#pragma unroll
+                                    for (int c = 0; c < 3; ++c) {
+                                        OutT* d = slow + (((size_t)c * p.n_slow + j) * crop + y_begin) * crop;
+                                        if (tg.l2hint & 2) bulk_store_hint(d, ssrc + c * sstep, bytes, pol);
+                                        else bulk_store(d, ssrc + c * sstep, bytes);
+                                    }
+                    } else {
                     const uint32_t bytes = (uint32_t)((size_t)rows * crop * 3 * esz);
                     if (tg.l2hint & 2) {
                         const uint64_t pol = l2_evict_first_policy();
@@ -619,6 +667,7 @@ __global__ void __launch_bounds__(kBlockThreads, 1) pva_tiled_kernel(const __gri
                             for (int j = 0; j < p.n_slow; ++j)
                                 if (p.slow_idx[j] == k) bulk_store(slow + ((size_t)j * crop + y_begin) * crop * 3, ssrc, bytes);
                     }
+                    }
                     bulk_commit();
                 }
                 if (++strip_it >= tg.out_bufs) strip_it = 0;
@@ -627,12 +676,24 @@ __global__ void __launch_bounds__(kBlockThreads, 1) pva_tiled_kernel(const __gri
                 named_bar(bar_strip, strip_threads);
                 const OutT* st = reinterpret_cast<const OutT*>(stage_out);
                 const int n_el = rows * crop * 3;
+                if (kPlanar) {
+                    const int plane_el = rows * crop;
+                    for (int idx = g_col; idx < n_el; idx += strip_threads) {
+                        const int c = idx / plane_el, rem = idx - c * plane_el;
+                        const OutT v = st[(size_t)c * tg.rps * crop + rem];
+                        fast[(((size_t)c * p.n_fast + k) * crop + y_begin) * crop + rem] = v;
+                        if (slow)
+                            for (int j = 0; j < p.n_slow; ++j)
+                                if (p.slow_idx[j] == k) slow[(((size_t)c * p.n_slow + j) * crop + y_begin) * crop + rem] = v;
+                    }
+                } else {
                 for (int idx = g_col; idx < n_el; idx += strip_threads) {
                     const OutT v = st[idx];
                     fast[((size_t)k * crop + y_begin) * crop * 3 + idx] = v;
                     if (slow)
                         for (int j = 0; j < p.n_slow; ++j)
                             if (p.slow_idx[j] == k) slow[((size_t)j * crop + y_begin) * crop * 3 + idx] = v;
+                }
                 }
                 named_bar(bar_strip, strip_threads);  // staging may be overwritten by the next tile
             }
@@ -662,8 +723,8 @@ int env_int(const char* name, int dflt) {
 
 // Choose rows-per-strip, ring depth and the shared-memory carve-up; false if nothing fits.
 bool plan_tiles(const KParams& p, int out_dtype, int layout, TileGeom* tg, const char** why) {
-    if (layout != kLayoutTHWC) {
-        *why = "tiled kernel writes the channels-last (T x S x S x C) layout only";
+    if (layout != kLayoutTHWC && layout != kLayoutCTHW) {
+        *why = "unknown output layout";
         return false;
     }
     if (p.C != 3) {
@@ -699,7 +760,9 @@ bool plan_tiles(const KParams& p, int out_dtype, int layout, TileGeom* tg, const
     const int pitch0 = max_cols + 15;
     const int pitch_max = pitch0 + 15;
     const int lut_bytes = 3 * 256 * 4;
-    const bool bulk_ok = (row_bytes % 16) == 0 && ((uintptr_t)p.fast_out % 16 == 0) &&
+    // a bulk store covers whole output rows (T x S x S x C) or whole rows of one channel plane (C x T x S x S)
+    const int store_unit = layout == kLayoutCTHW ? crop * esz : row_bytes;
+    const bool bulk_ok = (store_unit % 16) == 0 && ((uintptr_t)p.fast_out % 16 == 0) &&
                          (!p.slow_out || (uintptr_t)p.slow_out % 16 == 0);
 
     // candidate configurations in order of preference:
@@ -778,11 +841,11 @@ bool plan_tiles(const KParams& p, int out_dtype, int layout, TileGeom* tg, const
     return false;
 }
 
-template <typename OutT>
+template <typename OutT, bool kPlanar>
 cudaError_t launch_t(const TiledArgs& a, int norm, bool fastx, int grid, int smem, cudaStream_t stream) {
 #define PVA_TILED_CASE(N, F)                                                                          \
     if (norm == N && fastx == F) {                                                                    \
-        auto kern = pva_tiled_kernel<OutT, N, F>;                                                     \
+        auto kern = pva_tiled_kernel<OutT, N, F, kPlanar>;                                            \
         /* the opt-in shared-memory ceiling only ever needs raising (per device, per variant) */     \
         static int configured[64] = {};                                                               \
         int dev = 0;                                                                                  \
@@ -872,10 +935,14 @@ cudaError_t launch_tiled(KParams& p, int out_dtype, int layout, int norm, cudaSt
     cfg->grid = grid;
     cfg->block = kBlockThreads;
     cfg->tiles = a.g.total_tiles;
+    const bool planar = layout == kLayoutCTHW;
     switch (out_dtype) {
-        case 0: return launch_t<float>(a, kind, fastx, grid, smem, stream);
-        case 1: return launch_t<__half>(a, kind, fastx, grid, smem, stream);
-        case 2: return launch_t<__nv_bfloat16>(a, kind, fastx, grid, smem, stream);
+        case 0: return planar ? launch_t<float, true>(a, kind, fastx, grid, smem, stream)
+                              : launch_t<float, false>(a, kind, fastx, grid, smem, stream);
+        case 1: return planar ? launch_t<__half, true>(a, kind, fastx, grid, smem, stream)
+                              : launch_t<__half, false>(a, kind, fastx, grid, smem, stream);
+        case 2: return planar ? launch_t<__nv_bfloat16, true>(a, kind, fastx, grid, smem, stream)
+                              : launch_t<__nv_bfloat16, false>(a, kind, fastx, grid, smem, stream);
         default: return cudaErrorInvalidValue;
     }
 }

@@ -57,6 +57,12 @@ def test_random_shapes_tiled_equals_generic(seed, cuda_device):
             continue
         for a, b in zip(outs["generic"], outs["tiled"]):
             assert torch.equal(a, b), (shape, n_fast, alpha, crop, p)
+        # the reference's C x T x S x S memory order from the tiled kernel: same values, contiguous
+        tp = pva_b200.make_transform(**kw, out_dtype=torch.float32, norm_mode="exact", kernel="tiled",
+                                     channels_last=False)
+        for a, b in zip(outs["generic"], tp.explicit(clip, p)):
+            assert b.is_contiguous() and torch.equal(a, b), ("planar", shape, n_fast, alpha, crop, p)
+        assert _lib.last_launch_info()["kernel"] == 2
         # production mode on the same case stays inside the fp16 budget of the exact result
         t16 = pva_b200.make_transform(**kw, kernel="tiled")
         for a, b in zip(outs["generic"], t16.explicit(clip, p)):
@@ -87,3 +93,7 @@ def test_random_ragged_batches(cuda_device):
             res[kernel] = t.run_batch(clips, params)
         for a, b in zip(res["generic"], res["tiled"]):
             assert torch.equal(a, b)
+        tp = pva_b200.make_transform(**kw, out_dtype=torch.float32, norm_mode="exact", kernel="tiled",
+                                     channels_last=False)
+        for a, b in zip(res["generic"], tp.run_batch(clips, params)):
+            assert b.is_contiguous() and torch.equal(a, b)

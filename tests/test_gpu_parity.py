@@ -55,15 +55,16 @@ def supported(kernel, fn):
 
 
 @pytest.mark.parametrize("kernel", KERNELS)
+@pytest.mark.parametrize("channels_last", [False, True])
 @pytest.mark.parametrize("name", sorted(META))
-def test_golden_small_fp32_exact(name, kernel, cuda_device):
+def test_golden_small_fp32_exact(name, channels_last, kernel, cuda_device):
     m = META[name]
     kw = full_kwargs(m["kwargs"])
     clip = torch.from_numpy(DATA[f"{name}/in"])
     draws = draws_for_case(kw, m["shape"][2], m["shape"][3], m["seed"])
-    # the tiled kernel writes channels-last only; the logical C x T x S x S values are what is compared
+    # both memory orders (the reference's C x T x S x S and channels-last); the logical values are compared
     outs, info = supported(kernel, lambda: gpu_run(clip, draws, kw, out_dtype=torch.float32,
-                                                   channels_last=(kernel == "tiled"), norm_mode="exact", kernel=kernel))
+                                                   channels_last=channels_last, norm_mode="exact", kernel=kernel))
     c_ref = c_oracle_explicit(clip, draws, kw)
     for i, (o, c) in enumerate(zip(outs, c_ref)):
         assert np.array_equal(o, c), f"out{i}: CUDA differs from the C restatement"
@@ -72,14 +73,15 @@ def test_golden_small_fp32_exact(name, kernel, cuda_device):
 
 
 @pytest.mark.parametrize("kernel", KERNELS)
+@pytest.mark.parametrize("channels_last", [False, True])
 @pytest.mark.parametrize("name", sorted(load_large()))
-def test_golden_large_fp32_exact_is_bit_identical_to_reference(name, kernel, cuda_device):
+def test_golden_large_fp32_exact_is_bit_identical_to_reference(name, channels_last, kernel, cuda_device):
     e = load_large()[name]
     kw = full_kwargs(e["kwargs"])
     clip = synth_clip(e["shape"], e["seed"])
     draws = draws_for_case(kw, e["shape"][2], e["shape"][3], e["seed"])
     outs, info = supported(kernel, lambda: gpu_run(clip, draws, kw, out_dtype=torch.float32,
-                                                   channels_last=(kernel == "tiled"), norm_mode="exact", kernel=kernel))
+                                                   channels_last=channels_last, norm_mode="exact", kernel=kernel))
     assert info["kernel"] == {"generic": 1, "tiled": 2}[kernel]
     for o, g in zip(outs, e["outs"]):
         assert list(o.shape) == g["shape"]
