@@ -345,11 +345,19 @@ class SampleParams:
     ``'audio'`` and leaves ``'video'`` as raw uint8.  With ``subsample_on_worker=True`` the
     uint8 frame gather of ``UniformTemporalSubsample`` is done here, halving the bytes that
     cross PCIe for the usual 64 -> 32 frame case; the kernel then reads every frame it gets.
+
+    pytorchvideo's decoder hands over float32 frames holding the decoded bytes (0..255, whole
+    numbers).  ``narrow_float_frames=True`` (default) turns such a clip back into uint8 here
+    when, and only when, that is lossless -- the result of the transform is unchanged, the clip
+    crosses PCIe at a quarter of the size and takes the uint8 kernel.  A float clip with
+    fractional or out-of-range values is shipped as float32.
     """
 
-    def __init__(self, transform: GpuClipTransform, subsample_on_worker: bool = False):
+    def __init__(self, transform: GpuClipTransform, subsample_on_worker: bool = False,
+                 narrow_float_frames: bool = True):
         self.t = transform
         self.subsample_on_worker = subsample_on_worker
+        self.narrow_float_frames = narrow_float_frames
 
     def __call__(self, sample: dict) -> dict:
         video = sample["video"]
@@ -357,7 +365,11 @@ class SampleParams:
         p = self.t.sample_params(int(video.shape[2]), int(video.shape[3]))
         if self.subsample_on_worker:
             idx = torch.tensor(temporal_indices(int(video.shape[1]), self.t.num_frames), dtype=torch.long)
-            sample["video"] = torch.index_select(video, 1, idx)
+            video = sample["video"] = torch.index_select(video, 1, idx)
+        if self.narrow_float_frames and video.dtype == torch.float32:
+            as_bytes = video.to(torch.uint8)
+            if torch.equal(as_bytes.to(torch.float32), video):  # whole numbers in 0..255: nothing is lost
+                sample["video"] = as_bytes
         sample[PARAMS_KEY] = torch.tensor(p.as_row(), dtype=torch.int32)
         if "audio" in sample:
             del sample["audio"]

@@ -87,6 +87,21 @@ def test_sample_params_and_collate_cpu_side():
     assert isinstance(pva_b200.collate_raw_clips(ragged)["video"], list)
 
 
+def test_sample_params_narrows_decoder_style_float_frames_only_when_lossless():
+    """pytorchvideo's decoder hands over float32 frames holding whole byte values."""
+    t = pva_b200.make_transform(training=False, num_frames=4, crop_size=32, min_short_side_scale=32)
+    raw = torch.randint(0, 256, (3, 8, 40, 52), dtype=torch.uint8)
+    out = pva_b200.SampleParams(t)({"video": raw.float()})["video"]
+    assert out.dtype == torch.uint8 and torch.equal(out, raw)
+    for bad in (raw.float() + 0.25, raw.float() - 1.0, raw.float() * 1.5):  # fractional / below 0 / above 255
+        kept = pva_b200.SampleParams(t)({"video": bad.clone()})["video"]
+        assert kept.dtype == torch.float32 and torch.equal(kept, bad)
+    kept = pva_b200.SampleParams(t, narrow_float_frames=False)({"video": raw.float()})["video"]
+    assert kept.dtype == torch.float32
+    sub = pva_b200.SampleParams(t, subsample_on_worker=True)({"video": raw.float()})["video"]
+    assert sub.dtype == torch.uint8 and sub.shape[1] == 4
+
+
 def test_transform_validates_before_any_launch():
     t = pva_b200.make_transform()
     with pytest.raises(TypeError):
