@@ -135,3 +135,42 @@ def test_maximum_frame_counts(kernel, cuda_device):
     assert np.array_equal(fast.cpu().numpy(), rf) and np.array_equal(slow.cpu().numpy(), rs)
     with pytest.raises(NotImplementedError, match="n_fast"):
         pva_b200.make_transform(**dict(kw, num_frames=129), kernel=kernel).explicit(clip.cuda(), p)
+
+
+def test_column_cropped_tensor_map_loads_give_the_same_bits(cuda_device, monkeypatch):
+    """PVA_TILED_COLCROP=1 (experimental load path: four tensor maps per clip, only the window's
+    columns are fetched) must not change a single bit: frame corners, both flips, ragged batch,
+    clips at addresses that are only 4-byte aligned, H not a multiple of 4."""
+    kw = full_kwargs(dict(num_frames=4, slowfast_alpha=2))
+    t = pva_b200.make_transform(**kw, out_dtype=torch.float32, norm_mode="exact", kernel="tiled")
+    clips, params = [], []
+    for i, (h, size, off) in enumerate(((256, 256, 0), (256, 320, 4), (258, 300, 8), (256, 288, 12))):
+        c = synth_clip((3, 4 + (i % 2) * 2, h, 340), 900 + i)
+        oh, ow = pipeline.resized_hw(h, 340, size)
+        for top, left, flip in ((0, 0, False), (oh - 256, ow - 256, True), ((oh - 256) // 2, (ow - 256) // 3, False)):
+            n = c.numel()
+            dev = torch.empty(n + 16, dtype=torch.uint8, device="cuda")[off:off + n].view(c.shape)  # src % 16 == off
+            dev.copy_(c)
+            clips.append(dev)
+            params.append(ClipParams(size, oh, ow, top, left, flip))
+    monkeypatch.setenv("PVA_TILED_COLCROP", "0")
+    ref = [o.clone() for o in t.run_batch(clips, params)]
+    monkeypatch.setenv("PVA_TILED_COLCROP", "1")
+    got = t.run_batch(clips, params)
+    torch.cuda.synchronize()
+    for a, b in zip(ref, got):
+        assert torch.equal(a, b)
+    # and the production mode on a full-size same-shape batch (the benchmark's shape)
+    t16 = pva_b200.make_transform(**full_kwargs(dict(num_frames=32, slowfast_alpha=4)), kernel="tiled")
+    batch = torch.stack([synth_clip((3, 64, 256, 340), 40 + i) for i in range(2)]).cuda()
+    oh, ow = pipeline.resized_hw(256, 340, 297)
+    ps = [ClipParams(297, oh, ow, 11, 23, False), ClipParams(297, oh, ow, 0, ow - 256, True)]
+    monkeypatch.setenv("PVA_TILED_COLCROP", "0")
+    ref = [o.clone() for o in t16.run_batch(batch, ps)]
+    smem_linear = _lib.last_launch_info()["smem_bytes"]
+    monkeypatch.setenv("PVA_TILED_COLCROP", "1")
+    got = t16.run_batch(batch, ps)
+    torch.cuda.synchronize()
+    assert _lib.last_launch_info()["smem_bytes"] < smem_linear  # the cropped stages are smaller: the path was taken
+    for a, b in zip(ref, got):
+        assert torch.equal(a, b)
