@@ -411,6 +411,18 @@ def run_b200_arm(args):
         dist.destroy_process_group()
 
 
+AUTO_E2E_UPLOAD = "inplace"
+
+
+def upload_desc(h2d_bytes, B, shape, t):
+    whole = B * shape[0] * shape[1] * shape[2] * shape[3]
+    if h2d_bytes == whole:
+        return "H2D copy of whole clips"
+    if h2d_bytes == whole // shape[1] * t.num_frames:
+        return "H2D of the selected frames (strided DMA, pva_upload_selected_frames)"
+    return "no H2D copy: the kernel reads the selected frames' rows from the pinned batch over PCIe (h2d bytes = rows touched x full width)"
+
+
 def run_e2e(torch, pva_b200, t, wl, dev, dist, world, rank, args):
     """Public-API path with HOST buffers.  Every step: worker-side draws (SampleParams) and
     collate of raw uint8 clips into pinned memory were done up front (they are CPU-worker work
@@ -430,19 +442,21 @@ def run_e2e(torch, pva_b200, t, wl, dev, dist, world, rank, args):
         b["params"] = [pva_b200.ClipParams.from_row(r) for r in b["pva_params"].tolist()]
         host_batches.append(b)
     def measure(host_out):
-        # Strided selected-frame upload halves the H2D bytes.  On one GPU its many 2-D copies overlap
-        # worse with a concurrent full-size D2H stream than one flat copy does (3.13 vs 2.82 ms per
-        # step measured), so the host-to-host figure uploads whole clips there; with several ranks the
-        # host's memory system is the limit and fewer bytes win (4 GPUs: 5.13 vs 5.83 ms).  When the
-        # result stays on the device (no D2H leg) the selected-frame upload always pays (1.40 vs 2.41 ms).
-        if args.e2e_upload == "auto":
-            selected = (not host_out) or world > 1
-        else:
-            selected = args.e2e_upload == "selected"
+        # How the clips get to the device (--e2e-upload):
+        #   all       one flat copy of the whole pinned batch (134 MB)
+        #   selected  strided DMA of the frames the transform selects (67 MB); on one GPU its many 2-D
+        #             copies overlap worse with a concurrent full-size D2H stream than one flat copy
+        #             (3.13 vs 2.82 ms per step measured)
+        #   inplace   no copy: the kernel reads the selected frames' rows from the pinned batch over
+        #             PCIe (~59 MB), on a few SMs (1.22 vs 1.40 vs 2.46 ms per batch without the D2H leg)
+        mode = args.e2e_upload
+        if mode == "auto":
+            mode = AUTO_E2E_UPLOAD
         if args.upload_all_frames:
-            selected = False
+            mode = "all"
         staged = pva_b200.StagedPreprocess(t, B, shape, dev, depth=3, host_out=host_out,
-                                           upload_selected_frames=selected)
+                                           upload_selected_frames=(mode == "selected"),
+                                           read_in_place=(mode == "inplace"), max_ctas=args.e2e_ctas)
 
         def run(n):
             tickets = []
@@ -474,16 +488,14 @@ def run_e2e(torch, pva_b200, t, wl, dev, dist, world, rank, args):
     ms_dev, h2d_dev, _ = measure(host_out=False)
     return {"value": world * B * steps / (ms / 1000.0), "unit": UNIT, "h2d_bytes_per_step": int(h2d),
             "d2h_bytes_per_step": int(d2h), "steps": steps, "ms_per_step": ms / steps,
-            "path": "SampleParams -> collate_raw_clips (pinned) -> StagedPreprocess: H2D of "
-                    + ("whole clips" if h2d == B * int(torch.tensor(shape).prod()) else "the selected frames (strided DMA)")
+            "path": "SampleParams -> collate_raw_clips (pinned) -> StagedPreprocess: " + upload_desc(h2d, B, shape, t)
                     + " | fused kernel | D2H of [slow, fast] to pinned memory, 3 slots",
             # informational: the same pipeline when the result stays on the device for the model
             # (what a training step consumes), i.e. without the D2H leg
             "device_resident_result": {"value": world * B * steps / (ms_dev / 1000.0), "unit": UNIT,
                                        "ms_per_step": ms_dev / steps, "h2d_bytes_per_step": int(h2d_dev),
                                        "d2h_bytes_per_step": 0,
-                                       "path": "H2D of the frames the transform selects (pva_upload_selected_frames) "
-                                               "| fused kernel"}}
+                                       "path": upload_desc(h2d_dev, B, shape, t) + " | fused kernel"}}
 
 
 def main():
@@ -500,7 +512,9 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--overlap-streams", dest="overlap_streams", type=int, default=2,
                     help="also time the K steps issued round-robin on this many streams (informational; 0/1 = skip)")
-    ap.add_argument("--e2e-upload", dest="e2e_upload", choices=["auto", "all", "selected"], default="auto",
+    ap.add_argument("--e2e-ctas", dest="e2e_ctas", type=int, default=8,
+                    help="grid cap of launches that read pinned host clips in place (PvaPlan.max_ctas)")
+    ap.add_argument("--e2e-upload", dest="e2e_upload", choices=["auto", "all", "selected", "inplace"], default="auto",
                     help="e2e H2D leg: whole clips, only the selected frames, or auto (see run_e2e)")
     ap.add_argument("--upload-all-frames", action="store_true",
                     help="e2e: copy whole clips to the device instead of only the frames the transform selects")

@@ -82,7 +82,13 @@ typedef enum PvaSrcType { PVA_SRC_U8 = 0, PVA_SRC_F32 = 1 } PvaSrcType;
  * through the op chain of run.py:81-97:
  *   src, t_in, h, w  : the 'video' entry of the sample dict, C x T x H x W, contiguous, in DEVICE
  *                      memory; uint8, or float32 when plan->src_type == PVA_SRC_F32 (generic kernel;
- *                      any float values, evaluated with the reference's two divisions per tap)
+ *                      any float values, evaluated with the reference's two divisions per tap).
+ *                      src may also point into PAGE-LOCKED HOST memory that is mapped into the
+ *                      device's address space (cudaHostAlloc / cudaHostRegister, a pinned torch
+ *                      tensor): the kernel then reads the frames and rows it needs straight over
+ *                      PCIe and no host-to-device copy of the clip is needed at all -- for the usual
+ *                      64 -> 32 frame case less than half of the clip ever crosses the bus.  A few
+ *                      CTAs saturate the link: see PvaPlan.max_ctas.
  *   frame_idx        : HOST array of plan->n_fast indices into [0, t_in): the result of
  *                      UniformTemporalSubsample's linspace(0, T-1, n).long() (run.py:82).
  *                      Not closed-form in integers, hence a table.  Read during the call only.
@@ -110,6 +116,10 @@ typedef struct PvaClipDesc {
  *                      of PackPathway (run.py:59-63): slow[j] = fast[slow_idx[j]]
  *   crop             : crop_size; outputs are crop x crop
  *   mean, std        : Normalize (run.py:84)
+ *   max_ctas         : 0 = one CTA per SM.  A positive value caps the tiled kernel's grid; meant for
+ *                      launches that read their clips from mapped host memory, which are bound by
+ *                      PCIe (8 CTAs already saturate it) and should leave the other SMs to whatever
+ *                      else runs on the device.  No counterpart in the reference.
  */
 typedef struct PvaPlan {
     int32_t channels;
@@ -125,7 +135,8 @@ typedef struct PvaPlan {
     int32_t kernel;     /* PvaKernel  */
     int32_t src_type;   /* PvaSrcType */
     int32_t flags;      /* PVA_FLAG_* */
-    int32_t reserved[2];
+    int32_t max_ctas;   /* 0 = all SMs */
+    int32_t reserved;   /* must be 0 */
 } PvaPlan;
 
 /* What the last pva_preprocess call of this thread launched (for tests and bench.py). */

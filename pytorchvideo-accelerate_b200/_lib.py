@@ -71,7 +71,8 @@ class PvaPlan(ctypes.Structure):
         ("kernel", ctypes.c_int32),
         ("src_type", ctypes.c_int32),
         ("flags", ctypes.c_int32),
-        ("reserved", ctypes.c_int32 * 2),
+        ("max_ctas", ctypes.c_int32),
+        ("reserved", ctypes.c_int32),
     ]
 
 

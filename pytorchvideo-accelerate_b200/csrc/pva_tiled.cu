@@ -1097,6 +1097,11 @@ cudaError_t launch_tiled(KParams& p, int out_dtype, int layout, int norm, cudaSt
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     int grid = sms < a.g.total_tiles ? sms : a.g.total_tiles;
     if (grid > kMaxGrid) grid = kMaxGrid;
+    if (p.max_ctas > 0 && grid > p.max_ctas) grid = p.max_ctas;  // PvaPlan.max_ctas
+    {
+        const int cap = env_int("PVA_TILED_MAXGRID", 0);  // experiments
+        if (cap > 0 && grid > cap) grid = cap;
+    }
     {
         // cost model per tile: emit + control per output row, x-pass per source row of a strip
         const int tiles_per_clip = p.n_fast * a.g.bands;

@@ -25,10 +25,11 @@ from .transforms import GpuClipTransform
 
 class _Slot:
     def __init__(self, t: GpuClipTransform, batch: int, clip_shape: Sequence[int], device: torch.device,
-                 host_out: bool, selected_frames: bool):
+                 host_out: bool, selected_frames: bool, in_place: bool):
         c, t_in, h, w = clip_shape
         frames = t.num_frames if selected_frames else t_in
-        self.dev_in = torch.empty((batch, c, frames, h, w), dtype=torch.uint8, device=device)
+        # no device copy of the clips when the kernel reads the pinned host batch in place
+        self.dev_in = None if in_place else torch.empty((batch, c, frames, h, w), dtype=torch.uint8, device=device)
         self.raw_out = t.alloc_outputs(batch, device)
         self.host_out = [torch.empty(r.shape, dtype=r.dtype, pin_memory=True) for r in self.raw_out] if host_out else None
         self.in_ready = torch.cuda.Event()
@@ -45,11 +46,17 @@ class StagedPreprocess:
     With ``upload_selected_frames=True`` only the frames ``UniformTemporalSubsample`` selects
     (``run.py:82``) are copied to the device -- ``pva_upload_selected_frames`` folds the gather
     into strided DMA copies -- which halves the PCIe traffic of the usual 64 -> 32 frame case; the
-    kernel then reads every frame of the compact device clip."""
+    kernel then reads every frame of the compact device clip.
+
+    With ``read_in_place=True`` there is no H2D copy at all: the kernel is pointed at the pinned host
+    batch and fetches the selected frames' rows over PCIe itself (``include/pva_preproc.h``,
+    PvaClipDesc.src), on ``max_ctas`` SMs.  Fewer bytes cross the bus than with either copy (only the
+    rows the crop windows touch), and no copy engine is involved.  The caller must leave a submitted
+    host batch unchanged until its ticket has been collected."""
 
     def __init__(self, transform: GpuClipTransform, batch: int, clip_shape: Sequence[int],
                  device: Optional[torch.device] = None, depth: int = 3, host_out: bool = False,
-                 upload_selected_frames: bool = False):
+                 upload_selected_frames: bool = False, read_in_place: bool = False, max_ctas: int = 8):
         if depth < 2:
             raise ValueError("depth must be at least 2 to overlap anything")
         self.t = transform
@@ -57,8 +64,11 @@ class StagedPreprocess:
         self.batch = batch
         self.clip_shape = tuple(clip_shape)
         self.host_out = host_out
-        self.selected = bool(upload_selected_frames)
-        self.slots = [_Slot(transform, batch, clip_shape, self.device, host_out, self.selected) for _ in range(depth)]
+        self.in_place = bool(read_in_place)
+        self.max_ctas = int(max_ctas)
+        self.selected = bool(upload_selected_frames) and not self.in_place
+        self.slots = [_Slot(transform, batch, clip_shape, self.device, host_out, self.selected, self.in_place)
+                      for _ in range(depth)]
         idx = temporal_indices(self.clip_shape[1], transform.num_frames)
         self._idx = (ctypes.c_int32 * len(idx))(*idx)
         self._lib = _lib.load_library()
@@ -66,13 +76,18 @@ class StagedPreprocess:
         self.s_run = torch.cuda.Stream(self.device)
         self.s_out = torch.cuda.Stream(self.device)
         self._n = 0
-        self.h2d_bytes = self.slots[0].dev_in.numel()  # bytes that actually cross PCIe per batch
+        self._reading: list = []  # in place: (kernel-done event, pinned batch) of kernels that may still be reading
+        # bytes that cross PCIe per batch: the copy's size, or (in place) what the last submitted batch's
+        # kernel reads -- full-width source rows of the selected frames that its crop windows touch
+        self.h2d_bytes = 0 if self.in_place else self.slots[0].dev_in.numel()
         self.d2h_bytes = sum(r.numel() * r.element_size() for r in self.slots[0].raw_out) if host_out else 0
 
     def submit(self, host_clips: torch.Tensor, params: Sequence[ClipParams]) -> int:
         if tuple(host_clips.shape) != (self.batch,) + self.clip_shape or host_clips.dtype != torch.uint8:
             raise ValueError(f"expected uint8 clips of shape {(self.batch,) + self.clip_shape}")
         slot = self.slots[self._n % len(self.slots)]
+        if self.in_place:
+            return self._submit_in_place(slot, host_clips, params)
         with torch.cuda.stream(self.s_in):
             if slot.used:
                 self.s_in.wait_event(slot.kernel_done)  # the kernel that read this slot has finished
@@ -104,6 +119,37 @@ class StagedPreprocess:
                 self.s_out.wait_event(slot.kernel_done)
                 for h, r in zip(slot.host_out, slot.raw_out):
                     h.copy_(r, non_blocking=True)
+                slot.out_ready.record(self.s_out)
+        slot.used = True
+        ticket = self._n
+        self._n += 1
+        return ticket
+
+    def _submit_in_place(self, slot: _Slot, host_clips: torch.Tensor, params: Sequence[ClipParams]) -> int:
+        if not host_clips.is_pinned():
+            raise ValueError("read_in_place needs a pinned host batch (pin_memory())")
+        c, _t_in, h, w = self.clip_shape
+        rows = 0
+        for p in params:
+            fh, _fw = _lib.source_footprint(h, w, p.oh, p.ow, p.top, p.left, self.t.crop_size)
+            rows += fh
+        self.h2d_bytes = c * self.t.num_frames * rows * w
+        with torch.cuda.stream(self.s_run):
+            if slot.used and self.host_out:
+                self.s_run.wait_event(slot.out_ready)  # the previous result has left the slot
+            prepared = self.t.prepare_batch(host_clips, params, out=slot.raw_out, clips_ready=True,
+                                            max_ctas=self.max_ctas, device=self.device)
+            prepared.launch_raw(self.s_run.cuda_stream)
+            slot.kernel_done = torch.cuda.Event()
+            slot.kernel_done.record(self.s_run)
+            # the pinned batch stays referenced until the kernel that reads it has finished
+            self._reading = [(e, v) for e, v in self._reading if not e.query()]
+            self._reading.append((slot.kernel_done, host_clips))
+        if self.host_out:
+            with torch.cuda.stream(self.s_out):
+                self.s_out.wait_event(slot.kernel_done)
+                for h_, r in zip(slot.host_out, slot.raw_out):
+                    h_.copy_(r, non_blocking=True)
                 slot.out_ready.record(self.s_out)
         slot.used = True
         ticket = self._n

@@ -144,9 +144,10 @@ class GpuClipTransform:
             tab = self._idx_cache[t_in] = _IdxTable(temporal_indices(t_in, self.num_frames))
         return tab
 
-    def _plan(self, src_dtype: torch.dtype = torch.uint8, clips_ready: bool = False) -> _lib.PvaPlan:
+    def _plan(self, src_dtype: torch.dtype = torch.uint8, clips_ready: bool = False, max_ctas: int = 0) -> _lib.PvaPlan:
         plan = _lib.PvaPlan()
         plan.flags = _lib.PVA_FLAG_CLIPS_READY if clips_ready else 0
+        plan.max_ctas = int(max_ctas)
         plan.channels = len(self.mean)
         plan.n_fast = self.num_frames
         plan.n_slow = self.n_slow
@@ -186,11 +187,18 @@ class GpuClipTransform:
         return t.permute(0, 4, 1, 2, 3) if self.channels_last else t
 
     def prepare_batch(self, clips: Union[torch.Tensor, Sequence[torch.Tensor]], params: Sequence[ClipParams],
-                      out: Optional[Sequence[torch.Tensor]] = None, clips_ready: bool = False) -> "PreparedBatch":
+                      out: Optional[Sequence[torch.Tensor]] = None, clips_ready: bool = False,
+                      max_ctas: int = 0, device: Union[None, str, torch.device] = None) -> "PreparedBatch":
         """Validate a batch and build its descriptor table once; ``.launch()`` then costs a
         single C call.  ``clips``: a ``B x C x T x H x W`` uint8 cuda tensor or a sequence of
         ``C x T x H x W`` uint8 cuda tensors (ragged shapes allowed).  ``out`` may supply raw
         output buffers from :meth:`alloc_outputs`.
+
+        PINNED host clips (``tensor.pin_memory()``) are accepted as well and read IN PLACE: the
+        kernel fetches the frames and rows it needs over PCIe, no copy of the clip is made
+        (``include/pva_preproc.h``, PvaClipDesc.src).  Such a launch is PCIe-bound; ``max_ctas``
+        (e.g. 8) keeps it from occupying every SM while it waits for the bus.  The caller keeps
+        the host clips unchanged until the launch has run.
 
         ``clips_ready=True`` sets ``PVA_FLAG_CLIPS_READY`` (``include/pva_preproc.h``): say so when
         the clip bytes were complete before the previous kernel on the launch stream started (they
@@ -203,14 +211,19 @@ class GpuClipTransform:
             raise ValueError(f"{n} clips but {len(params)} parameter rows")
         if n == 0:
             raise ValueError("empty batch")
-        device = clip_list[0].device
-        if device.type != "cuda":
-            raise ValueError("device-resident clips required; use __call__ / GpuPreprocess for host clips")
+        src_device = clip_list[0].device
+        if src_device.type == "cuda":
+            device = src_device
+        else:
+            if not all(v.is_pinned() for v in clip_list):
+                raise ValueError("host clips must be page-locked (pin_memory()) to be read in place; "
+                                 "use __call__ / GpuPreprocess to have pageable clips copied")
+            device = torch.device(device) if device is not None else self._device_for(clip_list[0])
         descs = (_lib.PvaClipDesc * n)()
         keep = []
         for i, (v, p) in enumerate(zip(clip_list, params)):
             self._check_clip(v)
-            if v.device != device:
+            if v.device != src_device:
                 raise ValueError("all clips of a batch must live on one device")
             if not v.is_contiguous():
                 v = v.contiguous()
@@ -228,7 +241,7 @@ class GpuClipTransform:
             d.oh, d.ow, d.top, d.left, d.flip = p.oh, p.ow, p.top, p.left, int(p.flip)
         if out is None:
             out = self.alloc_outputs(n, device)
-        return PreparedBatch(self, descs, n, keep, list(out), device, clip_list[0].dtype, clips_ready)
+        return PreparedBatch(self, descs, n, keep, list(out), device, clip_list[0].dtype, clips_ready, max_ctas)
 
     def run_batch(self, clips: Union[torch.Tensor, Sequence[torch.Tensor]], params: Sequence[ClipParams],
                   out: Optional[Sequence[torch.Tensor]] = None,
@@ -277,14 +290,14 @@ class PreparedBatch:
 
     def __init__(self, transform: GpuClipTransform, descs, n: int, clips: List[torch.Tensor],
                  out: List[torch.Tensor], device: torch.device, src_dtype: torch.dtype = torch.uint8,
-                 clips_ready: bool = False):
+                 clips_ready: bool = False, max_ctas: int = 0):
         self.t = transform
         self.descs = descs
         self.n = n
         self.clips = clips
         self.raw_out = out
         self.device = device
-        self.plan = transform._plan(src_dtype, clips_ready)
+        self.plan = transform._plan(src_dtype, clips_ready, max_ctas)
         self._plan_ref = ctypes.byref(self.plan)
         self.slow_raw, self.fast_raw = (out[0], out[1]) if transform.n_slow else (None, out[-1])
         self._fast_ptr = self.fast_raw.data_ptr()
@@ -310,7 +323,8 @@ class PreparedBatch:
             s = stream if stream is not None else torch.cuda.current_stream(self.device)
             self.launch_raw(s.cuda_stream)
         for v in self.clips:  # inputs must outlive the asynchronous launch on this stream
-            v.record_stream(s)
+            if v.is_cuda:
+                v.record_stream(s)  # (pinned host clips read in place: the caller keeps them, see prepare_batch)
         return self.outputs
 
 
@@ -401,15 +415,25 @@ class GpuPreprocess:
     (``run.py:251-253``).  Host clips are copied to the rank's device first (pinned memory
     makes that copy asynchronous).  Each rank preprocesses only its own batches: the path
     shards by clip and needs no collective.
+
+    ``read_in_place=True``: a pinned uint8 batch (``DataLoader(pin_memory=True)``) is not copied
+    at all -- the kernel reads the selected frames' rows from host memory over PCIe on ``max_ctas``
+    SMs, which leaves the rest of the device to the model.  Pageable or float batches take the
+    copy path as before.
     """
 
     def __init__(self, transform: GpuClipTransform, device: Union[None, str, torch.device] = None,
-                 upload_selected_frames: bool = False):
+                 upload_selected_frames: bool = False, read_in_place: bool = False, max_ctas: int = 8):
         self.t = transform
         self.device = torch.device(device) if device is not None else transform.device
         # copy only the frames UniformTemporalSubsample selects (strided DMA, include/pva_preproc.h):
         # half the PCIe bytes for 64 -> 32 frames; needs a stacked, contiguous host batch
         self.upload_selected_frames = bool(upload_selected_frames)
+        # read_in_place: no copy at all when the batch is pinned (DataLoader(pin_memory=True)) -- the
+        # kernel fetches the frames and rows it needs over PCIe, on max_ctas SMs
+        self.read_in_place = bool(read_in_place)
+        self.max_ctas = int(max_ctas)
+        self._in_flight: List[tuple] = []  # (event, host clips) of launches that may still be reading
 
     def _upload_selected(self, video: torch.Tensor, dev: torch.device) -> torch.Tensor:
         b, c, t_in, h, w = video.shape
@@ -438,6 +462,16 @@ class GpuPreprocess:
         # is not a kernel: the launch is ordered after it in full); device tensors may have just been
         # produced by a kernel of the caller, so they get the conservative ordering
         from_host = (not video.is_cuda) if isinstance(video, torch.Tensor) else all(not v.is_cuda for v in video)
+        host_list = [video] if isinstance(video, torch.Tensor) else list(video)
+        if (self.read_in_place and from_host and all(v.is_pinned() and v.dtype == torch.uint8 for v in host_list)):
+            self._in_flight = [(e, v) for e, v in self._in_flight if not e.query()]
+            out = self.t.prepare_batch(video, params, clips_ready=True, max_ctas=self.max_ctas, device=dev).launch()
+            done = torch.cuda.Event()
+            done.record(torch.cuda.current_stream(dev))
+            self._in_flight.append((done, video))  # the pinned clips stay ours until the kernel has read them
+            batch["video"] = out if self.t.is_slowfast else out[0]
+            del batch[PARAMS_KEY]
+            return batch
         if (self.upload_selected_frames and isinstance(video, torch.Tensor) and not video.is_cuda
                 and video.dtype == torch.uint8 and video.is_contiguous()):
             clips = self._upload_selected(video, dev)

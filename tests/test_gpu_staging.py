@@ -30,14 +30,15 @@ def test_upload_selected_frames_is_the_temporal_gather(cuda_device):
     assert lib.pva_upload_selected_frames(clip.data_ptr(), dst.data_ptr(), 3, 5, 40, 52, arr, 2, None) == -1
 
 
-@pytest.mark.parametrize("selected", [False, True])
+@pytest.mark.parametrize("upload", ["all", "selected", "inplace"])
 @pytest.mark.parametrize("host_out", [False, True])
-def test_staged_pipeline_matches_direct_calls(host_out, selected, cuda_device):
+def test_staged_pipeline_matches_direct_calls(host_out, upload, cuda_device):
     kw = dict(min_short_side_scale=128, max_short_side_scale=160, crop_size=128, num_frames=8, training=True)
     t = pva_b200.make_transform(**kw)
     shape = (3, 16, 128, 172)
     staged = pva_b200.StagedPreprocess(t, 4, shape, cuda_device, depth=2, host_out=host_out,
-                                       upload_selected_frames=selected)
+                                       upload_selected_frames=(upload == "selected"),
+                                       read_in_place=(upload == "inplace"), max_ctas=5)
     torch.manual_seed(3)
     batches = []
     for b in range(5):  # more batches than slots: slots are reused
@@ -78,6 +79,40 @@ def test_gpu_preprocess_with_selected_frame_upload(cuda_device):
     b = pva_b200.GpuPreprocess(t, cuda_device)(dict(batch))["video"]
     torch.cuda.synchronize()
     assert all(torch.equal(x, y) for x, y in zip(a, b))
+
+
+def test_pinned_host_clips_are_read_in_place(cuda_device):
+    """A pinned host clip is a legal PvaClipDesc.src: same bits as from a device copy, on both kernels,
+    with a capped grid, ragged batch; pageable host memory is refused before any launch."""
+    from pva_b200 import _lib
+
+    kw = dict(num_frames=8, slowfast_alpha=4, crop_size=96, min_short_side_scale=96, max_short_side_scale=128,
+              training=True)
+    torch.manual_seed(21)
+    host = [synth_clip((3, 12 + i, 100 + 4 * i, 132), 300 + i).pin_memory() for i in range(3)]
+    for kernel in ("tiled", "generic"):
+        t = pva_b200.make_transform(**kw, out_dtype=torch.float32, norm_mode="exact", kernel=kernel)
+        params = [t.sample_params(v.shape[2], v.shape[3]) for v in host]
+        want = [o.clone() for o in t.run_batch([v.cuda() for v in host], params)]
+        got = t.prepare_batch(host, params, max_ctas=3, device=cuda_device).launch()
+        torch.cuda.synchronize()
+        assert all(torch.equal(g, w) for g, w in zip(got, want))
+        if kernel == "tiled":
+            assert _lib.last_launch_info()["grid"] == 3
+    with pytest.raises(ValueError, match="page-locked"):
+        t.prepare_batch([synth_clip((3, 12, 100, 132), 1)], params[:1])
+    # GpuPreprocess: a pinned batch is not copied, a pageable one is -- same result
+    t = pva_b200.make_transform(**kw)
+    sp = pva_b200.SampleParams(t)
+    samples = [sp({"video": synth_clip((3, 16, 128, 172), 70 + i), "label": i}) for i in range(3)]
+    batch = pva_b200.collate_raw_clips(samples)
+    pre = pva_b200.GpuPreprocess(t, cuda_device, read_in_place=True, max_ctas=4)
+    a = pre(dict(batch, video=batch["video"].pin_memory()))["video"]
+    assert _lib.last_launch_info()["grid"] == 4
+    b = pre(dict(batch))["video"]  # pageable: copy path
+    c = pva_b200.GpuPreprocess(t, cuda_device)(dict(batch))["video"]
+    torch.cuda.synchronize()
+    assert all(torch.equal(x, y) and torch.equal(x, z) for x, y, z in zip(a, b, c))
 
 
 def test_back_to_back_launches_into_the_same_outputs_keep_stream_order(cuda_device):
