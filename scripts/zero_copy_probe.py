@@ -65,3 +65,19 @@ for _ in range(10):
 e1.record()
 torch.cuda.synchronize()
 print(f"H2D copy of whole clips + kernel: {e0.elapsed_time(e1) / 10:.3f} ms per batch")
+
+# ---- outputs written in place as well: [slow, fast] in pinned host memory, one kernel does everything
+os.environ.pop("PVA_TILED_MAXGRID", None)
+host_out = [torch.empty(r.shape, dtype=r.dtype).pin_memory() for r in pb.raw_out]
+for ctas in (8, 16, 32, 148):
+    pbh = t.prepare_batch(host, params, out=host_out, clips_ready=True, max_ctas=ctas, device=dev)
+    pbh.launch()
+    torch.cuda.synchronize()
+    same = all(torch.equal(a.cpu(), t._logical(b)) for a, b in zip(ref, host_out))
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(10):
+        pbh.launch()
+    e1.record()
+    torch.cuda.synchronize()
+    print(f"host clips in, host result out, one kernel, {ctas} CTAs: identical={same}  {e0.elapsed_time(e1) / 10:.3f} ms per batch")
