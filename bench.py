@@ -249,6 +249,10 @@ def run_b200_arm(args):
     if world > 1:
         import torch.distributed as dist
 
+        # stdout carries exactly one JSON line: keep NCCL's version banner (NCCL_DEBUG=VERSION) off it;
+        # an explicit INFO/TRACE request is left alone
+        if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
+            os.environ["NCCL_DEBUG"] = "WARN"
         dist.init_process_group("nccl", device_id=dev)
 
     wl = dict(WORKLOADS[args.workload])
