@@ -64,6 +64,8 @@ def main():
     ap.add_argument("--batch", type=int, default=8)
     ap.add_argument("--accum", type=int, default=4)
     ap.add_argument("--workers", type=int, default=0, help="DataLoader workers per rank (0 = cores / ranks)")
+    ap.add_argument("--read-in-place", dest="read_in_place", action="store_true",
+                    help="--feed gpu: the kernel reads the pinned batch in place instead of a strided upload")
     args = ap.parse_args()
 
     rank, world, local = (int(os.environ.get(k, d)) for k, d in (("RANK", 0), ("WORLD_SIZE", 1), ("LOCAL_RANK", 0)))
@@ -93,7 +95,9 @@ def main():
         loader = torch.utils.data.DataLoader(ds, batch_size=args.batch, num_workers=workers, pin_memory=True,
                                              collate_fn=pva_b200.collate_raw_clips, persistent_workers=True,
                                              prefetch_factor=4)
-        to_device = pva_b200.GpuPreprocess(t, dev, upload_selected_frames=True)
+        # --read-in-place: no H2D copy, the kernel reads the pinned batch over PCIe on 8 SMs
+        to_device = pva_b200.GpuPreprocess(t, dev, upload_selected_frames=not args.read_in_place,
+                                           read_in_place=args.read_in_place, max_ctas=8)
     elif args.feed == "cpu":
         from bench import reference_cpu_transform  # bench.py's CPU-baseline leg: the reference's transform
 
@@ -140,7 +144,7 @@ def main():
         print(json.dumps({"feed": args.feed, "n_gpus": world, "batch_per_gpu": args.batch, "accum": args.accum,
                           "micro_steps": args.steps, "ms_per_micro_step": 1000 * dt / args.steps,
                           "clips_per_s": world * args.batch * args.steps / dt, "workers_per_rank": workers,
-                          "host_cores": cores, "model": "SlowFast-R50 (local restatement, random init), fp16 autocast"}),
+                          "host_cores": cores, "read_in_place": bool(args.read_in_place and args.feed == "gpu"), "model": "SlowFast-R50 (local restatement, random init), fp16 autocast"}),
               flush=True)
     del it
     if world > 1:
