@@ -42,6 +42,34 @@ def test_struct_sizes_match_the_header():
     assert ctypes.sizeof(_lib.PvaLaunchInfo) == 32
 
 
+def test_ctypes_layout_is_what_a_c_compiler_sees(tmp_path):
+    """Compile the header with gcc (plain C, as the include file promises) and compare sizeof /
+    offsetof of every field with the ctypes mirror in _lib.py."""
+    import shutil
+    import subprocess
+
+    gcc = shutil.which("gcc")
+    if gcc is None:
+        pytest.skip("no gcc")
+    structs = {"PvaClipDesc": _lib.PvaClipDesc, "PvaPlan": _lib.PvaPlan, "PvaLaunchInfo": _lib.PvaLaunchInfo}
+    lines = ['#include <stdio.h>', '#include <stddef.h>', '#include "pva_preproc.h"', "int main(void) {"]
+    for name, st in structs.items():
+        lines.append(f'printf("{name} %zu\\n", sizeof({name}));')
+        for field, _ in st._fields_:
+            lines.append(f'printf("{name}.{field} %zu\\n", offsetof({name}, {field}));')
+    lines += ["return 0;", "}"]
+    src = tmp_path / "layout.c"
+    src.write_text("\n".join(lines))
+    exe = tmp_path / "layout"
+    subprocess.run([gcc, "-std=c99", "-Wall", "-Werror", "-I", os.path.join(ROOT, "include"), str(src), "-o", str(exe)],
+                   check=True)
+    seen = dict(line.split() for line in subprocess.run([str(exe)], check=True, capture_output=True, text=True).stdout.splitlines())
+    for name, st in structs.items():
+        assert int(seen[name]) == ctypes.sizeof(st), name
+        for field, _ in st._fields_:
+            assert int(seen[f"{name}.{field}"]) == getattr(st, field).offset, f"{name}.{field}"
+
+
 def _plan(**over):
     p = _lib.PvaPlan()
     p.channels, p.n_fast, p.n_slow, p.crop = 3, 4, 0, 16
@@ -71,6 +99,7 @@ def _desc(**over):
     (dict(crop=0), {}, _lib.PVA_ERR_INVALID_ARGUMENT, "crop"),
     (dict(out_dtype=7), {}, _lib.PVA_ERR_INVALID_ARGUMENT, "out_dtype"),
     (dict(n_slow=2), {}, _lib.PVA_ERR_INVALID_ARGUMENT, "slow_out"),
+    (dict(max_ctas=-1), {}, _lib.PVA_ERR_INVALID_ARGUMENT, "max_ctas"),
     ({}, dict(src=None), _lib.PVA_ERR_INVALID_ARGUMENT, "src is NULL"),
     ({}, dict(oh=10, ow=30), _lib.PVA_ERR_CROP_TOO_LARGE, "larger than input image size"),
     ({}, dict(top=5), _lib.PVA_ERR_INVALID_ARGUMENT, "crop window"),
