@@ -249,10 +249,9 @@ def run_b200_arm(args):
     if world > 1:
         import torch.distributed as dist
 
-        # stdout carries exactly one JSON line: keep NCCL's version banner (NCCL_DEBUG=VERSION) off it;
-        # an explicit INFO/TRACE request is left alone
-        if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
-            os.environ["NCCL_DEBUG"] = "WARN"
+        # stdout carries exactly one JSON line: NCCL logs there by default (its version banner, and
+        # everything NCCL_DEBUG asks for) -- send that to stderr instead, whatever the level
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         dist.init_process_group("nccl", device_id=dev)
 
     wl = dict(WORKLOADS[args.workload])
