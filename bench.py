@@ -249,10 +249,19 @@ def run_b200_arm(args):
     if world > 1:
         import torch.distributed as dist
 
-        # stdout carries exactly one JSON line: NCCL logs there by default (its version banner, and
-        # everything NCCL_DEBUG asks for) -- send that to stderr instead, whatever the level
-        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
-        dist.init_process_group("nccl", device_id=dev)
+        # stdout carries exactly one JSON line, but NCCL prints there while the communicator comes up
+        # (its version banner under the image's NCCL_DEBUG=VERSION): point fd 1 at stderr meanwhile
+        sys.stdout.flush()
+        saved = os.dup(1)
+        os.dup2(2, 1)
+        try:
+            dist.init_process_group("nccl", device_id=dev)
+            dist.barrier()
+            torch.cuda.synchronize(dev)
+        finally:
+            sys.stdout.flush()
+            os.dup2(saved, 1)
+            os.close(saved)
 
     wl = dict(WORKLOADS[args.workload])
     if args.batch:
