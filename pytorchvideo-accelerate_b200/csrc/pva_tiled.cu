@@ -1071,13 +1071,13 @@ bool tiled_supported(const KParams& p, int out_dtype, int layout, const char** w
 cudaError_t launch_tiled(KParams& p, int out_dtype, int layout, int norm, cudaStream_t stream, TiledConfig* cfg) {
     static thread_local TiledArgsCC a;  // 30 KB: keep it off the stack
     const char* why = "";
-    bool colcrop = colcrop_eligible(p);
-    if (!plan_tiles(p, out_dtype, layout, &a.g, &why, colcrop)) return cudaErrorInvalidConfiguration;
-    for (int i = 0; i < p.n_clips && a.g.colcrop; ++i)
-        if (!encode_clip_maps(p.clips[i], a.g.cc_bw[i], a.g.cc_ng[i], &a.maps[4 * i])) colcrop = false, a.g.colcrop = 0;
-    if (colcrop && !a.g.colcrop) {
+    if (!plan_tiles(p, out_dtype, layout, &a.g, &why, colcrop_eligible(p))) return cudaErrorInvalidConfiguration;
+    if (a.g.colcrop) {
+        bool encoded = true;
+        for (int i = 0; i < p.n_clips && encoded; ++i)
+            encoded = encode_clip_maps(p.clips[i], a.g.cc_bw[i], a.g.cc_ng[i], &a.maps[4 * i]);
         // the driver refused a map: plan again for the linear band copies
-        if (!plan_tiles(p, out_dtype, layout, &a.g, &why, false)) return cudaErrorInvalidConfiguration;
+        if (!encoded && !plan_tiles(p, out_dtype, layout, &a.g, &why, false)) return cudaErrorInvalidConfiguration;
     }
     // the fast x-path needs, for every clip of the launch: up-scaling or identity in x (so that
     // the taps of 4 adjacent outputs fit an aligned 8-byte window) and 4-byte aligned rows
