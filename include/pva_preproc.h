@@ -14,8 +14,14 @@
  *     the clips, the outputs and keeps them alive until the stream has run the launch
  *   - every function returns PVA_OK (0) or a negative PvaStatus and never throws or exits;
  *     pva_last_error_string() gives the text for the calling thread's last failure
- *   - launches are asynchronous on the caller's stream; the library keeps no state
- *     between calls (descriptors and small tables travel as kernel arguments)
+ *   - launches are asynchronous on the caller's stream.  No device-side state and no
+ *     allocations: descriptors and small tables travel as kernel arguments.  What the
+ *     library does keep, on the host: per calling thread, the text of the last error and the
+ *     PvaLaunchInfo of the last call; per process, two small per-device caches filled on first
+ *     use (SM count; the largest dynamic shared-memory size already opted into per kernel
+ *     variant), updated with atomics, so calls from several threads are safe.
+ *   - the library reads no environment variables (the PVA_TILED_* experiment switches exist
+ *     only in the separate -DPVA_EXPERIMENTS build that scripts/ uses)
  */
 #ifndef PVA_PREPROC_H_
 #define PVA_PREPROC_H_

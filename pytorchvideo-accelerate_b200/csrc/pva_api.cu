@@ -242,23 +242,26 @@ int pva_preprocess(const PvaClipDesc* clips, int32_t n_clips, const PvaPlan* pla
         kp.slow_out = slow_out ? static_cast<char*>(slow_out) + (size_t)done * kp.slow_clip_elems * esize : nullptr;
 
         bool use_tiled = false;
-        const char* why = "";
+        cudaError_t ce = cudaSuccess;
         if (plan->kernel != PVA_KERNEL_GENERIC) {
-            use_tiled = tiled_supported(kp, plan->out_dtype, plan->out_layout, &why);
-            if (!use_tiled && plan->kernel == PVA_KERNEL_TILED)
-                return fail(PVA_ERR_UNSUPPORTED, "tiled kernel cannot take this launch: %s", why);
-        }
-        cudaError_t ce;
-        if (use_tiled) {
             TiledConfig cfg = {};
-            ce = launch_tiled(kp, plan->out_dtype, plan->out_layout, plan->norm_mode, stream, &cfg);
-            g_info.kernel = PVA_KERNEL_TILED;
-            g_info.grid = cfg.grid;
-            g_info.block = cfg.block;
-            g_info.smem_bytes = cfg.smem_bytes;
-            g_info.rows_per_tile = cfg.rows_per_tile;
-            g_info.tiles += cfg.tiles;
-        } else {
+            const char* why = nullptr;
+            ce = launch_tiled(kp, plan->out_dtype, plan->out_layout, plan->norm_mode, stream, &cfg, &why);
+            use_tiled = why == nullptr;  // planned and launched (or the launch itself failed)
+            if (!use_tiled) {
+                if (plan->kernel == PVA_KERNEL_TILED)
+                    return fail(PVA_ERR_UNSUPPORTED, "tiled kernel cannot take this launch: %s", why);
+                ce = cudaSuccess;
+            } else {
+                g_info.kernel = PVA_KERNEL_TILED;
+                g_info.grid = cfg.grid;
+                g_info.block = cfg.block;
+                g_info.smem_bytes = cfg.smem_bytes;
+                g_info.rows_per_tile = cfg.rows_per_tile;
+                g_info.tiles += cfg.tiles;
+            }
+        }
+        if (!use_tiled) {
             int grid = 0, block = 0;
             ce = launch_generic(kp, plan->out_dtype, plan->out_layout, plan->norm_mode, stream, &grid, &block);
             g_info.kernel = PVA_KERNEL_GENERIC;

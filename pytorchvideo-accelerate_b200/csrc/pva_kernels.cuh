@@ -94,8 +94,10 @@ struct TiledConfig {
     int block;
     int tiles;
 };
-// Returns false when the tiled kernel cannot take this launch (reason in *why).
-bool tiled_supported(const KParams& p, int out_dtype, int layout, const char** why);
-cudaError_t launch_tiled(KParams& p, int out_dtype, int layout, int norm, cudaStream_t stream, TiledConfig* cfg);
+// Plans (once) and launches.  When the tiled kernel cannot take this launch nothing is enqueued,
+// *why names the reason and cudaErrorNotSupported comes back; otherwise *why is nullptr and the
+// result is the launch's.
+cudaError_t launch_tiled(const KParams& p, int out_dtype, int layout, int norm, cudaStream_t stream, TiledConfig* cfg,
+                         const char** why);
 
 }  // namespace pva

@@ -36,6 +36,7 @@
 #include <cuda.h>  // CUtensorMap and its enums only; the encoder is looked up through the runtime
 #include <stdlib.h>
 
+#include <atomic>
 #include <type_traits>
 
 #include "pva_kernels.cuh"
@@ -43,6 +44,23 @@
 namespace pva {
 
 namespace {
+
+// Experiment switches.  The production library reads NOTHING from the environment: every knob is a
+// compile-time constant and the measurement-only branches of the kernel (stores / loads / arithmetic
+// switched off, alternative load paths) are compiled out.  `make experiments` builds a second
+// library, scripts/libpva_preproc_exp.so, with -DPVA_EXPERIMENTS: there the same knobs are the
+// PVA_TILED_* environment variables the A/B scripts under scripts/ use.
+#ifdef PVA_EXPERIMENTS
+constexpr bool kExperiments = true;
+int knob_env(const char* name, int dflt) {
+    const char* v = getenv(name);
+    return v ? atoi(v) : dflt;
+}
+#define PVA_KNOB(name, dflt) knob_env("PVA_TILED_" name, dflt)
+#else
+constexpr bool kExperiments = false;
+#define PVA_KNOB(name, dflt) (dflt)
+#endif
 
 constexpr int kConsumerThreads = 512;
 // 16 consumer warps + one producer WARPGROUP (only its first warp works): setmaxnreg trades
@@ -301,6 +319,10 @@ __global__ void __launch_bounds__(kBlockThreads, 1)
     constexpr bool kUniformNa = kNormT == 1;
     const KParams& p = a.p;
     const TileGeom& tg = a.g;
+    // measurement-only switches (see kExperiments): compile-time constants in the production library
+    const int dbg = kExperiments ? tg.debug : 0;
+    const bool load_rows = kExperiments && tg.load_rows;
+    const int l2hint = kExperiments ? tg.l2hint : 3;
     // one "tile has landed" barrier per (stage, consumer group): with an odd ring depth a stage
     // alternates between the groups, and a group polling a shared barrier by parity could run two
     // phases ahead of it (bulk copies complete out of order) and take the other group's phase for its own
@@ -319,7 +341,7 @@ __global__ void __launch_bounds__(kBlockThreads, 1)
         for (int s = 0; s < kMaxStages * 2; ++s) {
             // bulk mode: the producer's arrive.expect_tx, the copies complete the tx count;
             // row mode: one cp.async-arrive per producer lane
-            mbar_init(smem_u32(&s_full[s]), tg.load_rows ? 32 : 1);
+            mbar_init(smem_u32(&s_full[s]), load_rows ? 32 : 1);
             if (s < kMaxStages) mbar_init(smem_u32(&s_empty[s]), kConsumerThreads / 32 / tg.groups);  // the warps of the group that consumed the tile
         }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -365,7 +387,7 @@ __global__ void __launch_bounds__(kBlockThreads, 1)
                 const ClipGeom& g = p.clips[clip_i];
                 src = g.src, W = g.w, H = g.h, T_in = g.t_in, sy = g.sy, top = g.top, idx_row = g.idx_row;
                 src_range(g.sx, g.left, g.left + crop - 1, g.w, ca, ncols);
-                pitch = tg.load_rows ? tg.pitch0 + ((W - tg.pitch0) & 15) : W;
+                pitch = load_rows ? tg.pitch0 + ((W - tg.pitch0) & 15) : W;
                 if constexpr (kColCrop) {
                     cc_bw = tg.cc_bw[clip_i], cc_ng = tg.cc_ng[clip_i];
                     cc_ksub = (3u * cc_ng * cc_bw + 127u) & ~127u;
@@ -382,18 +404,18 @@ __global__ void __launch_bounds__(kBlockThreads, 1)
             if constexpr (kColCrop) {
                 // four tensor copies, one per row residue; a box always delivers its full size
                 // (rows or words past the tensor's extent arrive as zeros and are never read)
-                if (lane == 0) mbar_arrive_expect_tx(bar, (tg.debug & 2) ? 0u : 12u * cc_ng * cc_bw);
+                if (lane == 0) mbar_arrive_expect_tx(bar, (dbg & 2) ? 0u : 12u * cc_ng * cc_bw);
                 __syncwarp();
-                if (lane < 4 && !(tg.debug & 2)) {
+                if (lane < 4 && !(dbg & 2)) {
                     const uint32_t delta = (uint32_t)(((uintptr_t)src + (size_t)lane * W) & 15);
                     tensor_load_4d(st_base + (uint32_t)lane * cc_ksub, &a.maps[clip_i * 4 + lane],
                                    (int)((((uint32_t)ca + delta) & ~15u) >> 2), ra >> 2, t_src, 0, bar, pol);
                 }
-            } else if (tg.load_rows) {
+            } else if (load_rows) {
                 // Column-cropped rows, one source row per lane and pass: each lane walks its row in
                 // 16-byte granules (global and shared side both aligned because pitch == W mod 16).
                 // Staged byte (rr, col) sits at plane base + (gc & 15) + rr * pitch + (col - ca).
-                if (!(tg.debug & 2)) {
+                if (!(dbg & 2)) {
                     const int n_rows_all = 3 * nrows;
                     for (int j = lane; j < n_rows_all; j += 32) {
                         const int c = j / nrows, rr = j - c * nrows;
@@ -420,17 +442,17 @@ __global__ void __launch_bounds__(kBlockThreads, 1)
                 uint32_t total = lane < 3 ? bytes : 0u;
                 total += __shfl_xor_sync(0xffffffffu, total, 1);
                 total += __shfl_xor_sync(0xffffffffu, total, 2);
-                if (tg.debug & 2) total = 0;
+                if (dbg & 2) total = 0;
                 if (lane == 0) mbar_arrive_expect_tx(bar, total);
                 __syncwarp();
-                if (lane < 3 && !(tg.debug & 2)) {
-                    if (tg.l2hint & 1) bulk_load_hint(st_base + (uint32_t)lane * tg.plane_stride, g0 - sh, bytes, bar, pol);
+                if (lane < 3 && !(dbg & 2)) {
+                    if (l2hint & 1) bulk_load_hint(st_base + (uint32_t)lane * tg.plane_stride, g0 - sh, bytes, bar, pol);
                     else bulk_load(st_base + (uint32_t)lane * tg.plane_stride, g0 - sh, bytes, bar);
                 }
             }
             if (++s == n_stages) s = 0, ph ^= 1u;
         }
-        if (tg.load_rows) asm volatile("cp.async.wait_all;" ::: "memory");  // no copy may outlive the CTA
+        if (load_rows) asm volatile("cp.async.wait_all;" ::: "memory");  // no copy may outlive the CTA
         return;
     }
 
@@ -488,7 +510,7 @@ __global__ void __launch_bounds__(kBlockThreads, 1)
             const ClipGeom& g = p.clips[clip_i];
             src = g.src, W = g.w, H = g.h, T_in = g.t_in, idx_row = g.idx_row;
             // staged pitch: the source pitch itself (band copies) or the cropped pitch congruent to it mod 16
-            pitch = tg.load_rows ? tg.pitch0 + ((W - tg.pitch0) & 15) : W;
+            pitch = load_rows ? tg.pitch0 + ((W - tg.pitch0) & 15) : W;
             // AFFINE: the row weights absorb the 2^24 of the subnormal trick and, when all
             // channels share it, the normalisation scale 1 / (255 std)
             const float wscale = (kNorm == kNormAffine) ? 16777216.0f * (kUniformNa ? p.na[0] : 1.0f) : 1.0f;
@@ -554,7 +576,7 @@ __global__ void __launch_bounds__(kBlockThreads, 1)
         // every thread polls: measured faster than one poller per warp + __syncwarp (43.4 vs 46.0 us)
         mbar_wait(smem_u32(&s_full[2 * s + group]), ph);
 
-        if (active_col && rows > 0 && !(tg.debug & 4)) {
+        if (active_col && rows > 0 && !(dbg & 4)) {
             // staged address of (plane c, source row r, window start) = rowbase[c] + r * pitch
             // (kColCrop: rowbase[c] + the row's offset from the table)
             uint32_t rowbase[3];
@@ -696,7 +718,7 @@ __global__ void __launch_bounds__(kBlockThreads, 1)
             OutT* fast = reinterpret_cast<OutT*>(p.fast_out) + (size_t)clip_i * p.fast_clip_elems;
             OutT* slow = p.slow_out ? reinterpret_cast<OutT*>(p.slow_out) + (size_t)clip_i * p.slow_clip_elems : nullptr;
             if (tg.bulk_store) {
-                if (!(tg.debug & 16)) fence_async_smem();  // generic-proxy writes of the strip -> visible to the async proxy
+                if (!(dbg & 16)) fence_async_smem();  // generic-proxy writes of the strip -> visible to the async proxy
                 // double-buffered: the other buffer's store (issued a tile ago) must have drained
                 // before anyone runs ahead into the next tile and overwrites it
                 if (g_col == 0) {
@@ -704,7 +726,7 @@ __global__ void __launch_bounds__(kBlockThreads, 1)
                     if (tg.out_bufs == 3) bulk_wait_read_but_one();  // the store before last has drained
                 }
                 named_bar(bar_strip, strip_threads);
-                if (g_col == 0 && rows > 0 && !(tg.debug & 1)) {
+                if (g_col == 0 && rows > 0 && !(dbg & 1)) {
                     if (!may_store) {
                         asm volatile("griddepcontrol.wait;" ::: "memory");
                         may_store = true;
@@ -718,7 +740,7 @@ __global__ void __launch_bounds__(kBlockThreads, 1)
 #pragma unroll
                         for (int c = 0; c < 3; ++c) {
                             OutT* d = fast + (((size_t)c * p.n_fast + k) * crop + y_begin) * crop;
-                            if (tg.l2hint & 2) bulk_store_hint(d, ssrc + c * sstep, bytes, pol);
+                            if (l2hint & 2) bulk_store_hint(d, ssrc + c * sstep, bytes, pol);
                             else bulk_store(d, ssrc + c * sstep, bytes);
                         }
                         if (slow)
@@ -727,12 +749,12 @@ __global__ void __launch_bounds__(kBlockThreads, 1)
 #pragma unroll
                                     for (int c = 0; c < 3; ++c) {
                                         OutT* d = slow + (((size_t)c * p.n_slow + j) * crop + y_begin) * crop;
-                                        if (tg.l2hint & 2) bulk_store_hint(d, ssrc + c * sstep, bytes, pol);
+                                        if (l2hint & 2) bulk_store_hint(d, ssrc + c * sstep, bytes, pol);
                                         else bulk_store(d, ssrc + c * sstep, bytes);
                                     }
                     } else {
                     const uint32_t bytes = (uint32_t)((size_t)rows * crop * 3 * esz);
-                    if (tg.l2hint & 2) {
+                    if (l2hint & 2) {
                         const uint64_t pol = l2_evict_first_policy();
                         bulk_store_hint(fast + ((size_t)k * crop + y_begin) * crop * 3, ssrc, bytes, pol);
                         if (slow)
@@ -794,11 +816,7 @@ void host_taps(float scale, int dst, int in_size, int* i0, int* i1) {
     *i1 = b;
 }
 
-int env_int(const char* name, int dflt) {
-    const char* v = getenv(name);
-    return v ? atoi(v) : dflt;
-}
-
+#ifdef PVA_EXPERIMENTS
 typedef CUresult (*TensorMapEncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                       const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
                                       CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
@@ -823,13 +841,13 @@ TensorMapEncodeFn tensor_map_encoder() {
 // four keep 16-byte alignment from plane to plane, up-scaling or identity in x (the aligned-window
 // x-pass), and a parameter block that can hold the maps.
 //
-// OFF unless PVA_TILED_COLCROP=1.  Measured on B200 (profiles/r1_ablation.md): it cuts the DRAM read
+// Experiments build only, and there OFF unless PVA_TILED_COLCROP=1.  Measured on B200 (profiles/r1_ablation.md): it cuts the DRAM read
 // bytes by about 20 %, but the TMA unit walks a box row by row (272-byte rows here, ~25 cycles each),
 // so the loads alone take 20.0 us per headline launch against 15.7 us for the linear band copies.
 // Net: 37.4 vs 35.7 us at batch 8, 130.3 vs 132.9 us at batch 32.  Kept, parity-tested, for shapes
 // where the window is a small part of a wide frame.
 bool colcrop_eligible(const KParams& p) {
-    if (!env_int("PVA_TILED_COLCROP", 0) || env_int("PVA_TILED_LOAD_ROWS", 0)) return false;
+    if (!PVA_KNOB("COLCROP", 0) || PVA_KNOB("LOAD_ROWS", 0)) return false;
     if (p.n_clips > kMaxCropClips) return false;
     for (int i = 0; i < p.n_clips; ++i) {
         const ClipGeom& g = p.clips[i];
@@ -837,6 +855,9 @@ bool colcrop_eligible(const KParams& p) {
     }
     return tensor_map_encoder() != nullptr;
 }
+#else
+bool colcrop_eligible(const KParams&) { return false; }
+#endif
 
 // Choose rows-per-strip, ring depth and the shared-memory carve-up; false if nothing fits.
 bool plan_tiles(const KParams& p, int out_dtype, int layout, TileGeom* tg, const char** why, bool want_colcrop = false) {
@@ -872,7 +893,7 @@ bool plan_tiles(const KParams& p, int out_dtype, int layout, TileGeom* tg, const
         host_taps(g.sx, g.left + crop - 1, g.w, &b0, &b1);
         max_cols = max_cols > (b1 - a0 + 1) ? max_cols : (b1 - a0 + 1);
     }
-    const int load_rows = env_int("PVA_TILED_LOAD_ROWS", 0);
+    const int load_rows = PVA_KNOB("LOAD_ROWS", 0);
     bool colcrop = want_colcrop;
     // row mode: rows of a staged plane must not overlap; a copy spills up to 15 bytes on either side
     const int pitch0 = max_cols + 15;
@@ -887,8 +908,8 @@ bool plan_tiles(const KParams& p, int out_dtype, int layout, TileGeom* tg, const
     // (consumer groups, rows per strip, input stages, staging buffers per strip)
     static const int kCand[][4] = {{2, 8, 3, 1}, {1, 4, 2, 3}, {1, 4, 3, 2}, {1, 4, 2, 2}, {1, 4, 2, 1}, {1, 2, 3, 2},
                                    {1, 2, 2, 2}, {1, 2, 2, 1}, {1, 1, 2, 2}, {1, 1, 2, 1}};
-    const int force_rps = env_int("PVA_TILED_RPS", 0), force_bufs = env_int("PVA_TILED_OUTBUFS", 0),
-              force_stages = env_int("PVA_TILED_STAGES", 0), force_groups = env_int("PVA_TILED_GROUPS", 0);
+    const int force_rps = PVA_KNOB("RPS", 0), force_bufs = PVA_KNOB("OUTBUFS", 0),
+              force_stages = PVA_KNOB("STAGES", 0), force_groups = PVA_KNOB("GROUPS", 0);
     for (const auto& cand : kCand) {
         const int groups = cand[0], rps = cand[1], stages = cand[2], out_bufs = bulk_ok ? cand[3] : 1;
         if (force_groups && groups != force_groups) continue;
@@ -987,7 +1008,7 @@ bool plan_tiles(const KParams& p, int out_dtype, int layout, TileGeom* tg, const
         tg->bulk_store = bulk_ok ? 1 : 0;
         tg->total_tiles = p.n_clips * p.n_fast * bands;
         tg->na_uniform = (p.na[0] == p.na[1] && p.na[1] == p.na[2]) ? 1 : 0;
-        tg->debug = env_int("PVA_TILED_DEBUG", 0);
+        tg->debug = PVA_KNOB("DEBUG", 0);
         tg->colcrop = colcrop ? 1 : 0;
         return true;
     }
@@ -995,17 +1016,45 @@ bool plan_tiles(const KParams& p, int out_dtype, int layout, TileGeom* tg, const
     return false;
 }
 
+#ifdef PVA_EXPERIMENTS
+using LaunchArgs = TiledArgsCC;
+#else
+using LaunchArgs = TiledArgs;  // the column-cropped variant is not part of the production library
+#endif
+
+// Per-device facts, looked up once per process (relaxed atomics: racing threads store the same value).
+constexpr int kMaxDevices = 64;
+int sm_count(int dev) {
+    static std::atomic<int> cached[kMaxDevices];
+    if (dev >= 0 && dev < kMaxDevices) {
+        const int v = cached[dev].load(std::memory_order_relaxed);
+        if (v > 0) return v;
+    }
+    int sms = 148;
+    if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) {
+        (void)cudaGetLastError();
+        sms = 148;
+    }
+    if (dev >= 0 && dev < kMaxDevices) cached[dev].store(sms, std::memory_order_relaxed);
+    return sms;
+}
+
 template <typename OutT, int N, bool F, bool kPlanar, bool kColCrop, typename Args>
-cudaError_t launch_one(const Args& a, int grid, int smem, cudaStream_t stream) {
+cudaError_t launch_one(const Args& a, int dev, int grid, int smem, cudaStream_t stream) {
     auto kern = pva_tiled_kernel<OutT, N, F, kPlanar, kColCrop>;
-    // the opt-in shared-memory ceiling only ever needs raising (per device, per variant)
-    static int configured[64] = {};
-    int dev = 0;
-    cudaGetDevice(&dev);
-    if (dev < 0 || dev >= 64 || configured[dev] < smem) {
+    // The opt-in shared-memory ceiling only ever needs raising (per device, per variant).  This is
+    // the one piece of process-wide state the library keeps: a high-water mark per device, updated
+    // with relaxed atomics (two threads racing here both make the same idempotent call).
+    static std::atomic<int> configured[kMaxDevices];
+    const bool tracked = dev >= 0 && dev < kMaxDevices;
+    if (!tracked || configured[dev].load(std::memory_order_relaxed) < smem) {
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
         if (e != cudaSuccess) return e;
-        if (dev >= 0 && dev < 64) configured[dev] = smem;
+        if (tracked) {
+            int seen = configured[dev].load(std::memory_order_relaxed);
+            while (seen < smem && !configured[dev].compare_exchange_weak(seen, smem, std::memory_order_relaxed)) {
+            }
+        }
     }
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(grid);
@@ -1021,16 +1070,18 @@ cudaError_t launch_one(const Args& a, int grid, int smem, cudaStream_t stream) {
 }
 
 template <typename OutT, bool kPlanar>
-cudaError_t launch_t(const TiledArgsCC& a, int norm, bool fastx, int grid, int smem, cudaStream_t stream) {
+cudaError_t launch_t(const LaunchArgs& a, int norm, bool fastx, int dev, int grid, int smem, cudaStream_t stream) {
+#ifdef PVA_EXPERIMENTS
     if (a.g.colcrop) {  // implies fastx
-        if (norm == 0) return launch_one<OutT, 0, true, kPlanar, true, TiledArgsCC>(a, grid, smem, stream);
-        if (norm == 1) return launch_one<OutT, 1, true, kPlanar, true, TiledArgsCC>(a, grid, smem, stream);
-        if (norm == 2) return launch_one<OutT, 2, true, kPlanar, true, TiledArgsCC>(a, grid, smem, stream);
+        if (norm == 0) return launch_one<OutT, 0, true, kPlanar, true, TiledArgsCC>(a, dev, grid, smem, stream);
+        if (norm == 1) return launch_one<OutT, 1, true, kPlanar, true, TiledArgsCC>(a, dev, grid, smem, stream);
+        if (norm == 2) return launch_one<OutT, 2, true, kPlanar, true, TiledArgsCC>(a, dev, grid, smem, stream);
         return cudaErrorInvalidValue;
     }
+#endif
     const TiledArgs& b = a;
 #define PVA_TILED_CASE(N, F) \
-    if (norm == N && fastx == F) return launch_one<OutT, N, F, kPlanar, false, TiledArgs>(b, grid, smem, stream);
+    if (norm == N && fastx == F) return launch_one<OutT, N, F, kPlanar, false, TiledArgs>(b, dev, grid, smem, stream);
     PVA_TILED_CASE(0, false)
     PVA_TILED_CASE(0, true)
     PVA_TILED_CASE(1, false)
@@ -1041,6 +1092,7 @@ cudaError_t launch_t(const TiledArgsCC& a, int norm, bool fastx, int grid, int s
     return cudaErrorInvalidValue;
 }
 
+#ifdef PVA_EXPERIMENTS
 // The four residue-class tensors of one clip (see tensor_load_4d).
 bool encode_clip_maps(const ClipGeom& g, int bw, int ng, CUtensorMap* maps) {
     TensorMapEncodeFn enc = tensor_map_encoder();
@@ -1054,31 +1106,41 @@ bool encode_clip_maps(const ClipGeom& g, int bw, int ng, CUtensorMap* maps) {
         const cuuint32_t estr[4] = {1, 1, 1, 1};
         if (enc(&maps[k], CU_TENSOR_MAP_DATA_TYPE_UINT32, 4, reinterpret_cast<void*>(row_k - delta), dims, strides, box,
                 estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
-                (CUtensorMapL2promotion)env_int("PVA_TILED_CC_PROMO", 0),
+                (CUtensorMapL2promotion)PVA_KNOB("CC_PROMO", 0),
                 CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
             return false;
     }
     return true;
 }
+#endif
 
 }  // namespace
 
-bool tiled_supported(const KParams& p, int out_dtype, int layout, const char** why) {
-    TileGeom tg;
-    return plan_tiles(p, out_dtype, layout, &tg, why);
-}
-
-cudaError_t launch_tiled(KParams& p, int out_dtype, int layout, int norm, cudaStream_t stream, TiledConfig* cfg) {
-    static thread_local TiledArgsCC a;  // 30 KB: keep it off the stack
-    const char* why = "";
-    if (!plan_tiles(p, out_dtype, layout, &a.g, &why, colcrop_eligible(p))) return cudaErrorInvalidConfiguration;
+cudaError_t launch_tiled(const KParams& p, int out_dtype, int layout, int norm, cudaStream_t stream, TiledConfig* cfg,
+                         const char** why) {
+    // The argument block (~14 KB; ~30 KB with the experiments' tensor maps) lives on this call's
+    // stack: nothing survives the call.
+    LaunchArgs a;
+    *why = nullptr;
+    const char* reason = "";
+    // one plan per launch: it both decides whether the tiled kernel can take the shapes and carves
+    // up shared memory
+    if (!plan_tiles(p, out_dtype, layout, &a.g, &reason, colcrop_eligible(p))) {
+        *why = reason;
+        return cudaErrorNotSupported;
+    }
+#ifdef PVA_EXPERIMENTS
     if (a.g.colcrop) {
         bool encoded = true;
         for (int i = 0; i < p.n_clips && encoded; ++i)
             encoded = encode_clip_maps(p.clips[i], a.g.cc_bw[i], a.g.cc_ng[i], &a.maps[4 * i]);
         // the driver refused a map: plan again for the linear band copies
-        if (!encoded && !plan_tiles(p, out_dtype, layout, &a.g, &why, false)) return cudaErrorInvalidConfiguration;
+        if (!encoded && !plan_tiles(p, out_dtype, layout, &a.g, &reason, false)) {
+            *why = reason;
+            return cudaErrorNotSupported;
+        }
     }
+#endif
     // the fast x-path needs, for every clip of the launch: up-scaling or identity in x (so that
     // the taps of 4 adjacent outputs fit an aligned 8-byte window) and 4-byte aligned rows
     bool fastx = true;
@@ -1088,27 +1150,33 @@ cudaError_t launch_tiled(KParams& p, int out_dtype, int layout, int norm, cudaSt
     }
     static_cast<TiledArgs&>(a).p = p;
     // 1: wait for the previous kernel only before the first store (PVA_FLAG_CLIPS_READY); 2: wait
-    // before touching memory at all; 0: no programmatic dependent launch
-    a.g.pdl = env_int("PVA_TILED_PDL", p.clips_ready ? 1 : 2);
-    a.g.l2hint = env_int("PVA_TILED_L2HINT", 3);  // clip bytes are read once, outputs are consumed later: stream both
-    int dev = 0, sms = 148;
+    // before touching memory at all.  The ordering of the stores is never negotiable.
+    a.g.pdl = p.clips_ready ? 1 : 2;
+#ifdef PVA_EXPERIMENTS
+    a.g.pdl = knob_env("PVA_TILED_PDL", a.g.pdl);  // 0 = no programmatic dependent launch at all
+#endif
+    a.g.l2hint = PVA_KNOB("L2HINT", 3);  // clip bytes are read once, outputs are consumed later: stream both
+    int dev = 0;
     cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    const int sms = sm_count(dev);
     int grid = sms < a.g.total_tiles ? sms : a.g.total_tiles;
     if (grid > kMaxGrid) grid = kMaxGrid;
     if (p.max_ctas > 0 && grid > p.max_ctas) grid = p.max_ctas;  // PvaPlan.max_ctas
     {
-        const int cap = env_int("PVA_TILED_MAXGRID", 0);  // experiments
+        const int cap = PVA_KNOB("MAXGRID", 0);
         if (cap > 0 && grid > cap) grid = cap;
     }
     {
-        // cost model per tile: emit + control per output row, x-pass per source row of a strip
+        // Equal tile counts per CTA: the kernel is bound by its writes, which are the same for every
+        // tile.  (Experiments: PVA_TILED_BALANCE=1 weights tiles by a compute-cost model instead --
+        // emit + control per output row, x-pass per source row of a strip; measured 2 us slower.)
         const int tiles_per_clip = p.n_fast * a.g.bands;
+        const bool balance = PVA_KNOB("BALANCE", 0) != 0;
         double total = 0.0;
-        static thread_local double w[kMaxClipsPerLaunch];
+        double w[kMaxClipsPerLaunch];
         for (int i = 0; i < p.n_clips; ++i) {
             const double src_rows_per_strip = a.g.rps * (double)p.clips[i].sy + 1.5;
-            w[i] = env_int("PVA_TILED_BALANCE", 0) ? 62.0 * a.g.rps + 70.0 * src_rows_per_strip : 1.0;
+            w[i] = balance ? 62.0 * a.g.rps + 70.0 * src_rows_per_strip : 1.0;
             total += w[i] * tiles_per_clip;
         }
         int clip = 0, t = 0;
@@ -1133,12 +1201,12 @@ cudaError_t launch_tiled(KParams& p, int out_dtype, int layout, int norm, cudaSt
     cfg->tiles = a.g.total_tiles;
     const bool planar = layout == kLayoutCTHW;
     switch (out_dtype) {
-        case 0: return planar ? launch_t<float, true>(a, kind, fastx, grid, smem, stream)
-                              : launch_t<float, false>(a, kind, fastx, grid, smem, stream);
-        case 1: return planar ? launch_t<__half, true>(a, kind, fastx, grid, smem, stream)
-                              : launch_t<__half, false>(a, kind, fastx, grid, smem, stream);
-        case 2: return planar ? launch_t<__nv_bfloat16, true>(a, kind, fastx, grid, smem, stream)
-                              : launch_t<__nv_bfloat16, false>(a, kind, fastx, grid, smem, stream);
+        case 0: return planar ? launch_t<float, true>(a, kind, fastx, dev, grid, smem, stream)
+                              : launch_t<float, false>(a, kind, fastx, dev, grid, smem, stream);
+        case 1: return planar ? launch_t<__half, true>(a, kind, fastx, dev, grid, smem, stream)
+                              : launch_t<__half, false>(a, kind, fastx, dev, grid, smem, stream);
+        case 2: return planar ? launch_t<__nv_bfloat16, true>(a, kind, fastx, dev, grid, smem, stream)
+                              : launch_t<__nv_bfloat16, false>(a, kind, fastx, dev, grid, smem, stream);
         default: return cudaErrorInvalidValue;
     }
 }

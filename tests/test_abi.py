@@ -153,3 +153,11 @@ def test_upload_helper_validates_without_a_gpu():
     assert lib.pva_upload_selected_frames(0x1000, 0x2000, 3, 4, 8, 8, idx, 2, None) == _lib.PVA_ERR_INVALID_ARGUMENT
     assert "frame_idx[1]=5" in _lib.last_error()
     assert lib.pva_upload_selected_frames(0x1000, 0x2000, 0, 4, 8, 8, idx, 2, None) == _lib.PVA_ERR_INVALID_ARGUMENT
+
+
+def test_production_library_reads_no_experiment_switches():
+    """The PVA_TILED_* switches (stores off, fences off, forced tile shapes ...) exist only in the
+    -DPVA_EXPERIMENTS build under scripts/: the shipped library must not even contain their names.
+    (tests/test_gpu_edges.py checks on a GPU that setting them changes nothing.)"""
+    data = open(_lib.library_path(), "rb").read()
+    assert b"PVA_TILED_" not in data

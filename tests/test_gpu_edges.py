@@ -1,5 +1,7 @@
 """Edge cases of the CUDA path: launch chunking, ragged index tables, odd crops, strong
 down-scaling, channel counts, and tiled-vs-generic equality.  Needs a B200: -m gpu."""
+import os
+
 import numpy as np
 import pytest
 import torch
@@ -137,40 +139,27 @@ def test_maximum_frame_counts(kernel, cuda_device):
         pva_b200.make_transform(**dict(kw, num_frames=129), kernel=kernel).explicit(clip.cuda(), p)
 
 
-def test_column_cropped_tensor_map_loads_give_the_same_bits(cuda_device, monkeypatch):
-    """PVA_TILED_COLCROP=1 (experimental load path: four tensor maps per clip, only the window's
-    columns are fetched) must not change a single bit: frame corners, both flips, ragged batch,
-    clips at addresses that are only 4-byte aligned, H not a multiple of 4."""
-    kw = full_kwargs(dict(num_frames=4, slowfast_alpha=2))
-    t = pva_b200.make_transform(**kw, out_dtype=torch.float32, norm_mode="exact", kernel="tiled")
-    clips, params = [], []
-    for i, (h, size, off) in enumerate(((256, 256, 0), (256, 320, 4), (258, 300, 8), (256, 288, 12))):
-        c = synth_clip((3, 4 + (i % 2) * 2, h, 340), 900 + i)
-        oh, ow = pipeline.resized_hw(h, 340, size)
-        for top, left, flip in ((0, 0, False), (oh - 256, ow - 256, True), ((oh - 256) // 2, (ow - 256) // 3, False)):
-            n = c.numel()
-            dev = torch.empty(n + 16, dtype=torch.uint8, device="cuda")[off:off + n].view(c.shape)  # src % 16 == off
-            dev.copy_(c)
-            clips.append(dev)
-            params.append(ClipParams(size, oh, ow, top, left, flip))
-    monkeypatch.setenv("PVA_TILED_COLCROP", "0")
-    ref = [o.clone() for o in t.run_batch(clips, params)]
-    monkeypatch.setenv("PVA_TILED_COLCROP", "1")
-    got = t.run_batch(clips, params)
-    torch.cuda.synchronize()
-    for a, b in zip(ref, got):
-        assert torch.equal(a, b)
-    # and the production mode on a full-size same-shape batch (the benchmark's shape)
-    t16 = pva_b200.make_transform(**full_kwargs(dict(num_frames=32, slowfast_alpha=4)), kernel="tiled")
-    batch = torch.stack([synth_clip((3, 64, 256, 340), 40 + i) for i in range(2)]).cuda()
-    oh, ow = pipeline.resized_hw(256, 340, 297)
-    ps = [ClipParams(297, oh, ow, 11, 23, False), ClipParams(297, oh, ow, 0, ow - 256, True)]
-    monkeypatch.setenv("PVA_TILED_COLCROP", "0")
-    ref = [o.clone() for o in t16.run_batch(batch, ps)]
-    smem_linear = _lib.last_launch_info()["smem_bytes"]
-    monkeypatch.setenv("PVA_TILED_COLCROP", "1")
-    got = t16.run_batch(batch, ps)
-    torch.cuda.synchronize()
-    assert _lib.last_launch_info()["smem_bytes"] < smem_linear  # the cropped stages are smaller: the path was taken
-    for a, b in zip(ref, got):
-        assert torch.equal(a, b)
+def test_environment_cannot_switch_off_stores_or_fences(cuda_device):
+    """PVA_TILED_DEBUG / PVA_TILED_PDL used to be read on every launch of the shipped library (1 = drop
+    every store, 16 = drop the proxy fence, PDL=1 = weaker ordering).  They are compiled out now: with
+    them set, a fresh process gets bit-identical output."""
+    import subprocess
+    import sys
+
+    code = (
+        "import sys, hashlib, torch; sys.path.insert(0, %r); import pva_b200\n"
+        "g = torch.Generator().manual_seed(3)\n"
+        "clips = torch.randint(0, 256, (2, 3, 16, 128, 172), dtype=torch.uint8, generator=g).cuda()\n"
+        "t = pva_b200.make_transform(min_short_side_scale=128, max_short_side_scale=160, crop_size=128, num_frames=8,"
+        " training=True, kernel='tiled')\n"
+        "torch.manual_seed(5); params = [t.sample_params(128, 172) for _ in range(2)]\n"
+        "slow, fast = t.run_batch(clips, params); torch.cuda.synchronize()\n"
+        "print(hashlib.sha256(fast.cpu().numpy().tobytes() + slow.cpu().numpy().tobytes()).hexdigest())\n"
+    ) % os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    digests = []
+    for extra in ({}, {"PVA_TILED_DEBUG": "1"}, {"PVA_TILED_DEBUG": "16", "PVA_TILED_PDL": "1", "PVA_TILED_RPS": "2"}):
+        env = {k: v for k, v in os.environ.items() if not k.startswith("PVA_")}
+        env.update(extra)
+        out = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, check=True).stdout
+        digests.append(out.strip().splitlines()[-1])
+    assert digests[0] == digests[1] == digests[2]
