@@ -9,18 +9,29 @@ A *step* is one pass of the hot path over one batch of synthetic uint8 clips: on
 rank runs the same per-rank batch on its own GPU (weak scaling, no data-path collective --
 SURVEY.md section 8e); rank 0 prints ONE JSON line.
 
+``value`` / ``ms_per_step`` / ``roofline``: K plain launches back to back on one stream between two
+CUDA events (barrier + synchronize on both sides).  Consecutive launches are chained by programmatic
+dependent launch, so a launch starts reading its clips while the previous one drains: elapsed / K is
+the STEADY-STATE time per launch (a throughput figure), not the duration of one launch in isolation.
+The isolated duration is reported next to it (``launch_us_isolated``: events around a single launch
+that is queued behind a filler kernel, so that no host time sits between the events; median of 50),
+and so is the host cost of one call (``host_us_per_call``).
+
 Keys beyond the base contract:
-  roofline     dominant kernel: algorithmic bytes per launch / average launch duration
-               (CUDA events over the timed region) against MEASURED_PEAKS.json hbm_gbs
-  cpu_baseline the oracle's CPU pipeline (restated reference transform) on the host cores,
-               bounded sample, rank 0 at N=1 only
+  roofline     dominant kernel: algorithmic bytes per launch / steady-state time per launch against
+               MEASURED_PEAKS.json hbm_gbs; ``traffic`` = measured steady-state DRAM bytes per launch
+               (profiles/traffic.json: ncu over consecutive launches on rotating buffers)
+  cpu_baseline the oracle's CPU pipeline (restated reference transform) on the host cores, bounded
+               samples, rank 0 at N=1 only: one single-thread process per core (``value``), one
+               process x one thread (``one_thread``), and the reference's own execution model, a
+               ``DataLoader(num_workers=cores, batch_size=B)`` with default_collate (``dataloader``)
   e2e          same metric through the public API with HOST buffers: pinned uint8 clips ->
-               H2D -> fused kernel -> D2H of [slow, fast] into pinned memory, every step
+               fused kernel (reads them in place over PCIe) -> D2H of [slow, fast] into pinned
+               memory, every step; ``ceiling`` = the same bytes moved with no preprocessing at all
   overlapped_launches
-               informational: the same K steps issued round-robin on two streams (independent
-               batches; the next launch's CTAs start on SMs the previous one has left).  `value`,
-               `ms_per_step` and `roofline` stay on the single-stream region, where elapsed / K is
-               the duration of one launch
+               informational: the same K steps issued round-robin on two streams
+  rank_ms_per_step
+               N > 1: min / median / max over ranks of the per-rank time per step
 
 ``--impl reference`` times the reference's CPU implementation of the path (oracle port: the
 reference itself is pure Python over pytorchvideo, which is not installable here) on all host
@@ -32,8 +43,8 @@ import argparse
 import json
 import os
 import statistics
+import subprocess
 import sys
-import threading
 import time
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
@@ -59,8 +70,54 @@ WORKLOADS = {
 }
 
 
+def workload_geometry(wl):
+    """(crop, n_fast, n_slow) of a workload from the reference factory's defaults (run.py:68-79)."""
+    kw = wl["kwargs"]
+    crop = kw.get("crop_size", 256)
+    n_fast = kw.get("num_frames", 32)
+    n_slow = n_fast // kw.get("slowfast_alpha", 4) if kw.get("is_slowfast", True) else 0
+    return crop, n_fast, n_slow
+
+
+def rotation_sets(wl):
+    """How many distinct input/output buffer sets the device-resident region rotates over, and the
+    bytes of one set: the working set must exceed L2 (timing rule)."""
+    B, shape = wl["batch"], wl["shape"]
+    crop, n_fast, n_slow = workload_geometry(wl)
+    in_bytes = B * shape[0] * shape[1] * shape[2] * shape[3]
+    out_bytes = B * shape[0] * (n_fast + n_slow) * crop * crop * 2
+    n_sets = max(4, -(-3 * L2_BYTES // (in_bytes + out_bytes)))
+    return n_sets, in_bytes, out_bytes
+
+
+def workload_config(name, wl, world):
+    """The `config` object: what is measured.  Identical in the b200 and the reference arm."""
+    n_sets, in_bytes, out_bytes = rotation_sets(wl)
+    return {"workload": name, "batch_per_gpu": wl["batch"], "global_batch": wl["batch"] * world,
+            "clip_shape": list(wl["shape"]), "transform": wl["kwargs"],
+            "parallelism": f"dp{world} (clips sharded per rank, no collective)",
+            "l2": f"GPU arm: inputs and outputs rotate over {n_sets} sets = {(in_bytes + out_bytes) * n_sets >> 20} MiB > L2"}
+
+
+def host_cores():
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
+def cpu_model():
+    try:
+        for line in open("/proc/cpuinfo"):
+            if line.lower().startswith("model name"):
+                return line.split(":", 1)[1].strip()
+    except OSError:
+        pass
+    return "unknown"
+
+
 # --------------------------------------------------------------------------------------
-# CPU arm (oracle port of the reference transform), duration-bounded, one process per core
+# CPU arm (oracle port of the reference transform), duration-bounded
 # --------------------------------------------------------------------------------------
 def reference_cpu_transform(**kwargs):
     """The reference's CPU transform (oracle restatement of run.py:68-102) for the CPU-baseline legs.
@@ -88,22 +145,20 @@ def _cpu_worker(widx, shape, kwargs, counter, go, stop):
             counter.value += 1
 
 
-def cpu_reference_throughput(workload, seconds, warm_seconds=2.0, max_procs=64):
-    """clips/s of the reference CPU pipeline using one single-threaded process per host core."""
+def cpu_reference_throughput(workload, seconds, warm_seconds=2.0, max_procs=64, procs=None):
+    """clips/s of the reference CPU pipeline using one single-threaded process per host core
+    (``procs=1``: one process x one thread, i.e. one DataLoader worker)."""
     import multiprocessing as mp
 
     ctx = mp.get_context("spawn")
-    try:
-        cores = len(os.sched_getaffinity(0))
-    except AttributeError:
-        cores = os.cpu_count() or 1
-    procs_n = max(1, min(cores, max_procs))
+    cores = host_cores()
+    procs_n = procs if procs else max(1, min(cores, max_procs))
     counter = ctx.Value("l", 0)
     go, stop = ctx.Event(), ctx.Event()
     wl = WORKLOADS[workload]
-    procs = [ctx.Process(target=_cpu_worker, args=(i, wl["shape"], wl["kwargs"], counter, go, stop), daemon=True)
-             for i in range(procs_n)]
-    for p in procs:
+    ps = [ctx.Process(target=_cpu_worker, args=(i, wl["shape"], wl["kwargs"], counter, go, stop), daemon=True)
+          for i in range(procs_n)]
+    for p in ps:
         p.start()
     time.sleep(0.5)
     go.set()
@@ -116,12 +171,82 @@ def cpu_reference_throughput(workload, seconds, warm_seconds=2.0, max_procs=64):
     time.sleep(seconds)
     c1, t1 = counter.value, time.perf_counter()
     stop.set()
-    for p in procs:
+    for p in ps:
         p.join(timeout=30)
         if p.is_alive():
             p.terminate()
     clips = c1 - c0
     return dict(value=clips / (t1 - t0), clips=clips, seconds=t1 - t0, cores=procs_n, host_cores=cores)
+
+
+class _SyntheticClips:
+    """In-memory stand-in for the reference's dataset (run.py:151-168 minus decode): every item is
+    a raw uint8 clip pushed through the transform in the worker, like LabeledVideoDataset does."""
+
+    def __init__(self, shape, kwargs, length):
+        self.shape, self.kwargs, self.length = tuple(shape), dict(kwargs), length
+        self.clip = None
+        self.transform = None
+
+    def __len__(self):
+        return self.length
+
+    def __getitem__(self, i):
+        import torch
+
+        if self.clip is None:  # first touch inside the worker
+            g = torch.Generator().manual_seed(1234 + (i % 97))
+            self.clip = torch.randint(0, 256, self.shape, dtype=torch.uint8, generator=g)
+            self.transform = reference_cpu_transform(**self.kwargs)
+        return self.transform({"video": self.clip, "label": i % 700})
+
+
+def cpu_dataloader_throughput(workload, seconds, warm_batches=2):
+    """clips/s of the reference's execution model (run.py:170-176): a torch DataLoader with one
+    worker per host core, batch_size = the workload's batch, default_collate, batches handed to the
+    main process through shared memory."""
+    import torch
+    from torch.utils.data import DataLoader
+
+    wl = WORKLOADS[workload]
+    workers = host_cores()
+    ds = _SyntheticClips(wl["shape"], wl["kwargs"], 1 << 20)
+    loader = DataLoader(ds, batch_size=wl["batch"], num_workers=workers, shuffle=False, pin_memory=False,
+                        multiprocessing_context="spawn", persistent_workers=False)
+    it = iter(loader)
+    for _ in range(warm_batches + -(-workers // wl["batch"])):
+        next(it)
+    n, t0 = 0, time.perf_counter()
+    while time.perf_counter() - t0 < seconds:
+        b = next(it)
+        v = b["video"]
+        assert (v[0] if isinstance(v, (list, tuple)) else v).shape[0] == wl["batch"]
+        n += wl["batch"]
+    t1 = time.perf_counter()
+    del it, loader
+    return dict(value=n / (t1 - t0), clips=n, seconds=t1 - t0, workers=workers)
+
+
+def cpu_baseline_block(workload, seconds, full=True):
+    r = cpu_reference_throughput(workload, seconds)
+    block = {
+        "value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": "port", "cpu_model": cpu_model(),
+        "sample": (f"{r['clips']} clips in {r['seconds']:.1f}s, oracle.pipeline.make_transform (restated "
+                   f"reference transform), {r['cores']} single-thread processes of {r['host_cores']} host cores")}
+    if full:
+        one = cpu_reference_throughput(workload, max(4.0, seconds / 3), warm_seconds=1.0, procs=1)
+        block["one_thread"] = {"value": one["value"], "unit": UNIT, "cores": 1,
+                               "sample": f"{one['clips']} clips in {one['seconds']:.1f}s, 1 process x 1 thread"}
+        try:
+            dl = cpu_dataloader_throughput(workload, max(6.0, seconds / 2))
+            block["dataloader"] = {
+                "value": dl["value"], "unit": UNIT, "cores": dl["workers"],
+                "sample": (f"{dl['clips']} clips in {dl['seconds']:.1f}s, torch DataLoader(num_workers={dl['workers']}, "
+                           f"batch_size={WORKLOADS[workload]['batch']}, default_collate) over an in-memory dataset: "
+                           "the reference's execution model, run.py:170-176")}
+        except Exception as e:  # noqa: BLE001 -- the baseline must not take the bench line down
+            block["dataloader"] = {"error": f"{type(e).__name__}: {e}"}
+    return block
 
 
 def run_reference_arm(args):
@@ -137,14 +262,15 @@ def run_reference_arm(args):
     r = cpu_reference_throughput(args.workload, seconds)
     ms_per_step = 1000.0 * wl["batch"] / r["value"]
     sample = (f"{r['clips']} clips of {wl['shape']} uint8 through oracle.pipeline.make_transform"
-              f"({wl['kwargs']}) in {r['seconds']:.1f}s on {r['cores']} single-thread processes")
+              f"({wl['kwargs']}) in {r['seconds']:.1f}s on {r['cores']} single-thread processes; "
+              "duration-bounded sample, step = one batch equivalent")
     line = {
         "impl": "reference", "metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": args.workload, "batch_per_step": wl["batch"], "clip_shape": list(wl["shape"]),
-                   "transform": wl["kwargs"], "note": "duration-bounded sample; step = one batch equivalent"},
-        "cpu_baseline": {"value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": "port", "sample": sample},
+        "config": workload_config(args.workload, wl, max(1, args.gpus)),
+        "cpu_baseline": {"value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": "port", "sample": sample,
+                         "cpu_model": cpu_model()},
         "e2e": {"value": r["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -152,54 +278,83 @@ def run_reference_arm(args):
 
 
 # --------------------------------------------------------------------------------------
-# clocks
+# clocks: sampled by a SEPARATE process, so that the sampler never competes with the launch loop
+# for the interpreter lock (an in-process NVML thread cost ~1.6 us per step of a 20-step region)
 # --------------------------------------------------------------------------------------
-_REASONS = {0x4: "sw_power_cap", 0x8: "hw_slowdown", 0x20: "sw_thermal_slowdown", 0x40: "hw_thermal_slowdown",
-            0x80: "hw_power_brake_slowdown", 0x2: "applications_clocks_setting", 0x10: "sync_boost"}
-
-
-class ClockSampler(threading.Thread):
-    """Samples SM clock and throttle reasons of one GPU through NVML while the timed region runs."""
-
-    def __init__(self, index, period=0.01):
-        super().__init__(daemon=True)
-        self.index, self.period = index, period
-        self.samples, self.reasons = [], set()
-        self.max_mhz = None
-        self._stop_evt = threading.Event()
-        self.ok = False
+_SAMPLER_CODE = r"""
+import json, select, sys, time
+idx, period = int(sys.argv[1]), float(sys.argv[2])
+R = {0x4: "sw_power_cap", 0x8: "hw_slowdown", 0x20: "sw_thermal_slowdown", 0x40: "hw_thermal_slowdown",
+     0x80: "hw_power_brake_slowdown", 0x2: "applications_clocks_setting", 0x10: "sync_boost"}
+out = {"ok": False, "samples": [], "max_mhz": None}
+try:
+    import pynvml as nv
+    nv.nvmlInit()
+    h = nv.nvmlDeviceGetHandleByIndex(idx)
+    out["max_mhz"] = nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM)
+    out["ok"] = True
+except Exception as e:
+    out["error"] = repr(e)
+print("ready", flush=True)
+while True:
+    if out["ok"]:
         try:
-            import pynvml
+            t = time.time()
+            mhz = nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)
+            mask = nv.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+            out["samples"].append([t, mhz, [n for b, n in R.items() if mask & b]])
+        except Exception:
+            pass
+    if select.select([sys.stdin], [], [], period)[0]:
+        break
+print(json.dumps(out), flush=True)
+"""
 
-            pynvml.nvmlInit()
-            self.nv = pynvml
-            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
-            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
-            self.ok = True
+
+class ClockSampler:
+    """SM clock and throttle reasons of one GPU, sampled through NVML by a child process while the
+    timed region runs.  ``mark()`` brackets the region on the shared wall clock; samples inside it
+    (or, for a region shorter than the period, the two samples around it) are reported."""
+
+    def __init__(self, index, period=0.002):
+        self.proc = None
+        try:
+            self.proc = subprocess.Popen([sys.executable, "-c", _SAMPLER_CODE, str(index), str(period)],
+                                         stdin=subprocess.PIPE, stdout=subprocess.PIPE, text=True)
+            self.proc.stdout.readline()  # "ready": NVML is up and the loop is running
         except Exception:  # noqa: BLE001
-            self.ok = False
+            self.proc = None
+        self.t0 = self.t1 = None
 
-    def run(self):
-        if not self.ok:
-            return
-        while not self._stop_evt.is_set():
-            try:
-                mhz = self.nv.nvmlDeviceGetClockInfo(self.h, self.nv.NVML_CLOCK_SM)
-                mask = self.nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
-                self.samples.append(mhz)
-                for bit, name in _REASONS.items():
-                    if mask & bit:
-                        self.reasons.add(name)
-            except Exception:  # noqa: BLE001
-                pass
-            time.sleep(self.period)
+    def mark_start(self):
+        self.t0 = time.time()
+
+    def mark_end(self):
+        self.t1 = time.time()
 
     def finish(self):
-        self._stop_evt.set()
-        if self.is_alive():
-            self.join(timeout=2)
-        return {"sm_mhz": statistics.median(self.samples) if self.samples else None, "sm_max_mhz": self.max_mhz,
-                "reasons": sorted(self.reasons), "samples": len(self.samples)}
+        res = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        if self.proc is None:
+            return res
+        try:
+            out, _ = self.proc.communicate("stop\n", timeout=10)
+            data = json.loads(out.strip().splitlines()[-1])
+        except Exception:  # noqa: BLE001
+            self.proc.kill()
+            return res
+        res["sm_max_mhz"] = data.get("max_mhz")
+        samples = data.get("samples", [])
+        inside = [s for s in samples if self.t0 is not None and self.t0 <= s[0] <= self.t1]
+        if not inside and samples and self.t0 is not None:
+            before = [s for s in samples if s[0] < self.t0][-1:]
+            after = [s for s in samples if s[0] > self.t1][:1]
+            inside = before + after
+        if inside:
+            res["sm_mhz"] = statistics.median(s[1] for s in inside)
+            res["reasons"] = sorted({r for s in inside for r in s[2]})
+            res["samples"] = len(inside)
+        res["sampler"] = "NVML in a child process, 2 ms period; samples inside (or bracketing) the timed region"
+        return res
 
 
 def physical_gpu_index(local_rank):
@@ -225,10 +380,30 @@ def measured_peak():
 
 
 def recorded_traffic(workload):
-    """DRAM bytes per launch of the dominant kernel from the committed ncu --set full capture."""
+    """Steady-state DRAM bytes per launch of the dominant kernel, measured with ncu over consecutive
+    launches on rotating buffers (profiles/traffic.json says how); None when not measured."""
     try:
-        return json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get(workload)
+        v = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get(workload)
+        return v if isinstance(v, (int, float)) else None
     except Exception:  # noqa: BLE001
+        return None
+
+
+def pin_to_rank_cores(local_rank, world):
+    """Give each rank its own contiguous share of the host cores: the launch loop of one rank must
+    not be descheduled in favour of another rank's helper threads inside a sub-millisecond timed
+    region (N = 8 measured 0.94 of the 1-GPU rate without this)."""
+    if world <= 1:
+        return None
+    try:
+        cores = sorted(os.sched_getaffinity(0))
+        per = len(cores) // world
+        if per < 1:
+            return None
+        mine = cores[local_rank * per:(local_rank + 1) * per]
+        os.sched_setaffinity(0, mine)
+        return mine
+    except (AttributeError, OSError):
         return None
 
 
@@ -238,11 +413,10 @@ def run_b200_arm(args):
     import pva_b200
     from pva_b200 import _lib
 
-    rank = int(os.environ.get("RANK", "0"))
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    rank, world, local_rank = pva_b200.rank_and_world()
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device (this path has no CPU fallback)")
+    pinned_cores = pin_to_rank_cores(local_rank, world)
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     dist = None
@@ -275,11 +449,9 @@ def run_b200_arm(args):
     C, crop, n_fast, n_slow = shape[0], t.crop_size, t.num_frames, t.n_slow
 
     # ---- synthetic, device-resident, rotated so the working set exceeds L2 ----
-    in_bytes = B * int(torch.tensor(shape).prod())
-    out_bytes = B * C * (n_fast + n_slow) * crop * crop * esize
-    n_sets = max(4, -(-3 * L2_BYTES // (in_bytes + out_bytes)))
-    gen = torch.Generator().manual_seed(1234 + rank)
-    torch.manual_seed(42 + rank)
+    n_sets, in_bytes, out_bytes = rotation_sets(wl)
+    gen = torch.Generator().manual_seed(pva_b200.rank_seed(1234, rank))
+    torch.manual_seed(pva_b200.rank_seed(42, rank))
     sets, algo_bytes = [], []
     for s in range(n_sets):
         clips = torch.randint(0, 256, (B,) + tuple(shape), dtype=torch.uint8, generator=gen).to(dev)
@@ -292,9 +464,10 @@ def run_b200_arm(args):
         algo_bytes.append(b)
     stream = torch.cuda.current_stream(dev)
     raw_stream = stream.cuda_stream
+    launchers = [s.launch_raw for s in sets]
 
     def step(i):
-        sets[i % n_sets].launch_raw(raw_stream)
+        launchers[i % n_sets](raw_stream)
 
     graph = None
     if args.graph:
@@ -315,7 +488,6 @@ def run_b200_arm(args):
             dist.barrier()
         torch.cuda.synchronize(dev)
 
-    sampler = ClockSampler(physical_gpu_index(local_rank))
     def run_steps(first, count):
         # exactly `count` steps: whole rotations come from the graph, the remainder are plain launches
         i = 0
@@ -326,37 +498,75 @@ def run_b200_arm(args):
             while count - i >= n_sets:
                 graph.replay()
                 first, i = first + n_sets, i + n_sets
-        while i < count:
-            step(first)
-            first, i = first + 1, i + 1
+        # the order of the plain launches is fixed before the clock starts
+        todo = [launchers[(first + j) % n_sets] for j in range(count - i)]
+        for fn in todo:
+            fn(raw_stream)
 
+    sampler = ClockSampler(physical_gpu_index(local_rank))
     run_steps(0, args.warmup)
     info = _lib.last_launch_info()
-    barrier()
-    sampler.start()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    sampler.mark_start()
     e0.record(stream)
     run_steps(args.warmup, args.steps)
     e1.record(stream)
     barrier()
+    sampler.mark_end()
     clocks = sampler.finish()
-    elapsed_ms = e0.elapsed_time(e1)
+    own_ms = e0.elapsed_time(e1)
+    elapsed_ms = own_ms
+    rank_stats = None
     if dist is not None:
-        tt = torch.tensor([elapsed_ms], device=dev, dtype=torch.float64)
-        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-        elapsed_ms = float(tt.item())
+        mine = torch.tensor([own_ms], device=dev, dtype=torch.float64)
+        every = [torch.zeros_like(mine) for _ in range(world)]
+        dist.all_gather(every, mine)
+        per_rank = [float(v.item()) / args.steps for v in every]
+        elapsed_ms = max(per_rank) * args.steps
+        rank_stats = {"min": min(per_rank), "median": statistics.median(per_rank), "max": max(per_rank),
+                      "slowest_rank": per_rank.index(max(per_rank))}
     ms_per_step = elapsed_ms / args.steps
     value = world * B * args.steps / (elapsed_ms / 1000.0)
     used = [(args.warmup + i) % n_sets for i in range(args.steps)]
     mean_algo = sum(algo_bytes[u] for u in used) / len(used)
 
+    # ---- host cost of one call: K calls into an empty queue, wall clock (nothing blocks: the
+    # launch queue is far deeper than K)
+    barrier()
+    k_host = min(max(args.steps, 10), 100)
+    todo = [launchers[j % n_sets] for j in range(k_host)]
+    h0 = time.perf_counter()
+    for fn in todo:
+        fn(raw_stream)
+    host_us = (time.perf_counter() - h0) * 1e6 / k_host
+    torch.cuda.synchronize(dev)
+
+    # ---- one launch in isolation: queued behind a filler (a plain device memset long enough to
+    # cover the host's enqueue time), so both events and the launch are already in the queue when
+    # the filler ends and no host time sits between the events
+    filler = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    iso = []
+    for j in range(50):
+        a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        filler.zero_()
+        a0.record(stream)
+        launchers[j % n_sets](raw_stream)
+        a1.record(stream)
+        torch.cuda.synchronize(dev)
+        iso.append(a0.elapsed_time(a1) * 1000.0)
+    del filler
+    launch_us_isolated = statistics.median(iso)
+
     peak, peak_src = measured_peak()
     achieved = mean_algo / (ms_per_step / 1000.0) / 1e9
-    traffic = recorded_traffic(args.workload)
+    traffic = recorded_traffic(args.workload) if not (args.batch or args.size or args.planar) else None
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                 "traffic": traffic, "peak_source": peak_src, "frac_of_nominal_8TBs": achieved / NOMINAL_HBM_GBS,
                 "algorithmic_bytes_per_launch": mean_algo,
-                "kernel": {1: "pva_generic_kernel", 2: "pva_tiled_kernel"}.get(info["kernel"], "?")}
+                "kernel": {1: "pva_generic_kernel", 2: "pva_tiled_kernel"}.get(info["kernel"], "?"),
+                "time_basis": "steady-state time per launch (K back-to-back launches / K; consecutive launches overlap)",
+                "isolated_launch_GBps": mean_algo / (launch_us_isolated * 1e-6) / 1e9}
 
     # ---- informational: the same K steps issued round-robin on two streams.  Consecutive batches are
     # independent, so the block scheduler starts the next launch's CTAs on SMs the previous launch has
@@ -395,27 +605,25 @@ def run_b200_arm(args):
     # ---- e2e: HOST buffers through the public API, copies inside the timed region ----------
     e2e = run_e2e(torch, pva_b200, t, wl, dev, dist, world, rank, args)
 
+    config = workload_config(args.workload, wl, world)
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": "f32", "data": "synthetic",
-        "config": {"workload": args.workload, "batch_per_gpu": B, "global_batch": B * world,
-                   "clip_shape": list(shape), "transform": kw, "out": "fp16 CTHW (the reference's memory order)" if args.planar else "fp16 THWC (channels_last_3d)",
-                   "norm_mode": args.norm_mode, "parallelism": f"dp{world} (clips sharded per rank, no collective)",
-                   "l2": f"{n_sets} rotating input/output sets = {(in_bytes + out_bytes) * n_sets >> 20} MiB > L2",
-                   "launch": info, "cuda_graph": bool(args.graph)},
-        "roofline": roofline, "e2e": e2e, "gpu_launches": args.steps * info["launches"], "clocks": clocks,
+        "dtype": "f32", "data": "synthetic", "config": config,
+        "impl_detail": {"out": "fp16 CTHW (the reference's memory order)" if args.planar else "fp16 THWC (channels_last_3d)",
+                        "norm_mode": args.norm_mode, "launch": info, "cuda_graph": bool(args.graph),
+                        "pinned_cores": pinned_cores},
+        "roofline": roofline, "launch_us_isolated": launch_us_isolated, "host_us_per_call": host_us,
+        "e2e": e2e, "gpu_launches": args.steps * info["launches"], "clocks": clocks,
     }
+    if rank_stats is not None:
+        line["rank_ms_per_step"] = rank_stats
     if overlapped is not None:
         line["overlapped_launches"] = overlapped
     if world == 1 and rank == 0 and not args.no_cpu_baseline:
-        del sets
+        del sets, launchers
         torch.cuda.empty_cache()
-        r = cpu_reference_throughput(args.workload, args.cpu_seconds)
-        line["cpu_baseline"] = {
-            "value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": "port",
-            "sample": (f"{r['clips']} clips in {r['seconds']:.1f}s, oracle.pipeline.make_transform (restated "
-                       f"reference transform), {r['cores']} single-thread processes of {r['host_cores']} host cores")}
+        line["cpu_baseline"] = cpu_baseline_block(args.workload, args.cpu_seconds, full=not args.cpu_baseline_short)
     if rank == 0:
         print(json.dumps(line), flush=True)
     if dist is not None:
@@ -435,12 +643,48 @@ def upload_desc(h2d_bytes, B, shape, t):
     return "no H2D copy: the kernel reads the selected frames' rows from the pinned batch over PCIe (h2d bytes = rows touched x full width)"
 
 
+def copy_only_ceiling(torch, dev, dist, world, B, steps, h2d_bytes, d2h_bytes):
+    """What the host link allows for this step's bytes with NO preprocessing: every step moves
+    ``h2d_bytes`` from pinned host memory to the device and ``d2h_bytes`` back into pinned host memory
+    with plain asynchronous copies, three slots, both directions in flight at once (PCIe is full
+    duplex), all ranks concurrently.  The end-to-end figure cannot exceed this on the same box."""
+    depth = 3
+    s_in, s_out = torch.cuda.Stream(dev), torch.cuda.Stream(dev)
+    h_in = [torch.empty(max(h2d_bytes, 1), dtype=torch.uint8, pin_memory=True) for _ in range(depth)]
+    d_in = [torch.empty(max(h2d_bytes, 1), dtype=torch.uint8, device=dev) for _ in range(depth)]
+    d_out = [torch.empty(max(d2h_bytes, 1), dtype=torch.uint8, device=dev) for _ in range(depth)]
+    h_out = [torch.empty(max(d2h_bytes, 1), dtype=torch.uint8, pin_memory=True) for _ in range(depth)]
+
+    def run(n):
+        for i in range(n):
+            k = i % depth
+            with torch.cuda.stream(s_in):
+                d_in[k].copy_(h_in[k], non_blocking=True)
+            with torch.cuda.stream(s_out):
+                h_out[k].copy_(d_out[k], non_blocking=True)
+        s_in.synchronize()
+        s_out.synchronize()
+
+    run(3)
+    if dist is not None:
+        dist.barrier()
+    torch.cuda.synchronize(dev)
+    t0 = time.perf_counter()
+    run(steps)
+    ms = (time.perf_counter() - t0) * 1000.0
+    if dist is not None:
+        tt = torch.tensor([ms], device=dev, dtype=torch.float64)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        ms = float(tt.item())
+    return world * B * steps / (ms / 1000.0), ms / steps
+
+
 def run_e2e(torch, pva_b200, t, wl, dev, dist, world, rank, args):
     """Public-API path with HOST buffers.  Every step: worker-side draws (SampleParams) and
     collate of raw uint8 clips into pinned memory were done up front (they are CPU-worker work
-    in the reference too); inside the timed region each step copies that step's pinned clips to
+    in the reference too); inside the timed region each step gets that step's pinned clips to
     the device, runs the fused kernel, and copies [slow, fast] back into pinned host memory.
-    StagedPreprocess overlaps the three phases of consecutive steps (PCIe is full duplex)."""
+    StagedPreprocess overlaps the phases of consecutive steps (PCIe is full duplex)."""
     B, shape = wl["batch"], wl["shape"]
     steps = max(5, min(args.steps, args.e2e_steps))
     gen = torch.Generator().manual_seed(99 + rank)
@@ -453,14 +697,13 @@ def run_e2e(torch, pva_b200, t, wl, dev, dist, world, rank, args):
         b["video"] = b["video"].pin_memory()
         b["params"] = [pva_b200.ClipParams.from_row(r) for r in b["pva_params"].tolist()]
         host_batches.append(b)
+
     def measure(host_out):
         # How the clips get to the device (--e2e-upload):
         #   all       one flat copy of the whole pinned batch (134 MB)
-        #   selected  strided DMA of the frames the transform selects (67 MB); on one GPU its many 2-D
-        #             copies overlap worse with a concurrent full-size D2H stream than one flat copy
-        #             (3.13 vs 2.82 ms per step measured)
+        #   selected  strided DMA of the frames the transform selects (67 MB)
         #   inplace   no copy: the kernel reads the selected frames' rows from the pinned batch over
-        #             PCIe (~59 MB), on a few SMs (1.22 vs 1.40 vs 2.46 ms per batch without the D2H leg)
+        #             PCIe (~59 MB), on a few SMs
         mode = args.e2e_upload
         if mode == "auto":
             mode = AUTO_E2E_UPLOAD
@@ -498,10 +741,18 @@ def run_e2e(torch, pva_b200, t, wl, dev, dist, world, rank, args):
 
     ms, h2d, d2h = measure(host_out=True)
     ms_dev, h2d_dev, _ = measure(host_out=False)
-    return {"value": world * B * steps / (ms / 1000.0), "unit": UNIT, "h2d_bytes_per_step": int(h2d),
+    value = world * B * steps / (ms / 1000.0)
+    ceil_value, ceil_ms = copy_only_ceiling(torch, dev, dist, world, B, steps, int(h2d), int(d2h))
+    return {"value": value, "unit": UNIT, "h2d_bytes_per_step": int(h2d),
             "d2h_bytes_per_step": int(d2h), "steps": steps, "ms_per_step": ms / steps,
             "path": "SampleParams -> collate_raw_clips (pinned) -> StagedPreprocess: " + upload_desc(h2d, B, shape, t)
                     + " | fused kernel | D2H of [slow, fast] to pinned memory, 3 slots",
+            # the same bytes per step and direction as plain pinned copies, no preprocessing: the
+            # host link's own limit on this box at this N
+            "ceiling": {"value": ceil_value, "unit": UNIT, "ms_per_step": ceil_ms,
+                        "what": "copy-only: h2d_bytes_per_step H2D + d2h_bytes_per_step D2H per step, pinned, "
+                                "3 slots, both directions concurrent, all ranks at once"},
+            "frac_of_ceiling": value / ceil_value if ceil_value else None,
             # informational: the same pipeline when the result stays on the device for the model
             # (what a training step consumes), i.e. without the D2H leg
             "device_resident_result": {"value": world * B * steps / (ms_dev / 1000.0), "unit": UNIT,
@@ -522,6 +773,8 @@ def main():
     ap.add_argument("--e2e-steps", dest="e2e_steps", type=int, default=40)
     ap.add_argument("--cpu-seconds", dest="cpu_seconds", type=float, default=12.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cpu-baseline-short", action="store_true",
+                    help="only the one-process-per-core CPU figure (skip the one-thread and DataLoader modes)")
     ap.add_argument("--overlap-streams", dest="overlap_streams", type=int, default=2,
                     help="also time the K steps issued round-robin on this many streams (informational; 0/1 = skip)")
     ap.add_argument("--e2e-ctas", dest="e2e_ctas", type=int, default=8,

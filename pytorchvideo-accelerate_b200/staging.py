@@ -23,6 +23,25 @@ from .geometry import ClipParams, temporal_indices
 from .transforms import GpuClipTransform
 
 
+def _flat_outputs(t: GpuClipTransform, batch: int, device, pin: bool):
+    """[slow_raw, fast_raw] (or [fast_raw]) as views of ONE contiguous byte buffer, so that a result
+    crosses PCIe as a single copy instead of one per pathway.  Returns (flat, views)."""
+    c, s = len(t.mean), t.crop_size
+    esz = torch.empty((), dtype=t.out_dtype).element_size()
+    frames = ([t.n_slow] if t.n_slow else []) + [t.num_frames]
+    sizes = [batch * f * s * s * c * esz for f in frames]
+    offs, total = [], 0
+    for b in sizes:
+        offs.append(total)
+        total += -(-b // 256) * 256  # every view starts 256-byte aligned (bulk stores need 16)
+    flat = torch.empty(total, dtype=torch.uint8, pin_memory=True) if pin else torch.empty(total, dtype=torch.uint8, device=device)
+    views = []
+    for f, o, b in zip(frames, offs, sizes):
+        shape = (batch, f, s, s, c) if t.channels_last else (batch, c, f, s, s)
+        views.append(flat[o:o + b].view(t.out_dtype).view(shape))
+    return flat, views
+
+
 class _Slot:
     def __init__(self, t: GpuClipTransform, batch: int, clip_shape: Sequence[int], device: torch.device,
                  host_out: bool, selected_frames: bool, in_place: bool):
@@ -30,11 +49,14 @@ class _Slot:
         frames = t.num_frames if selected_frames else t_in
         # no device copy of the clips when the kernel reads the pinned host batch in place
         self.dev_in = None if in_place else torch.empty((batch, c, frames, h, w), dtype=torch.uint8, device=device)
-        self.raw_out = t.alloc_outputs(batch, device)
-        self.host_out = [torch.empty(r.shape, dtype=r.dtype, pin_memory=True) for r in self.raw_out] if host_out else None
+        self.flat_out, self.raw_out = _flat_outputs(t, batch, device, pin=False)
+        self.host_flat, self.host_out = _flat_outputs(t, batch, device, pin=True) if host_out else (None, None)
         self.in_ready = torch.cuda.Event()
         self.kernel_done = torch.cuda.Event()
         self.out_ready = torch.cuda.Event()
+        self.released = None  # event recorded by release(): the consumer is done with raw_out
+        self.host_clips = None  # the pinned batch a queued copy or kernel may still be reading
+        self.consumer_stream = None  # stream that was current when result() handed out raw_out
         self.used = False
 
 
@@ -51,8 +73,16 @@ class StagedPreprocess:
     With ``read_in_place=True`` there is no H2D copy at all: the kernel is pointed at the pinned host
     batch and fetches the selected frames' rows over PCIe itself (``include/pva_preproc.h``,
     PvaClipDesc.src), on ``max_ctas`` SMs.  Fewer bytes cross the bus than with either copy (only the
-    rows the crop windows touch), and no copy engine is involved.  The caller must leave a submitted
-    host batch unchanged until its ticket has been collected."""
+    rows the crop windows touch), and no copy engine is involved.
+
+    Lifetime rules.  In every upload mode the host batch is read ASYNCHRONOUSLY (by a copy or by the
+    kernel itself): the caller must leave a submitted host batch unchanged until its ticket has been
+    collected with ``result()``; the pipeline keeps a reference to it until then, so the tensor is
+    not freed (and its pinned block not recycled by torch's host allocator) under a queued read.
+    With ``host_out=False`` ``result()`` hands out views of the slot's device buffers; the slot is
+    rewritten ``depth`` submits later.  ``submit`` therefore makes the kernel stream wait for the
+    stream that was current when the ticket was collected -- or, if the consumer works on other
+    streams, for the event of an explicit ``release(ticket)`` -- before it overwrites the slot."""
 
     def __init__(self, transform: GpuClipTransform, batch: int, clip_shape: Sequence[int],
                  device: Optional[torch.device] = None, depth: int = 3, host_out: bool = False,
@@ -80,7 +110,7 @@ class StagedPreprocess:
         # bytes that cross PCIe per batch: the copy's size, or (in place) what the last submitted batch's
         # kernel reads -- full-width source rows of the selected frames that its crop windows touch
         self.h2d_bytes = 0 if self.in_place else self.slots[0].dev_in.numel()
-        self.d2h_bytes = sum(r.numel() * r.element_size() for r in self.slots[0].raw_out) if host_out else 0
+        self.d2h_bytes = self.slots[0].flat_out.numel() if host_out else 0  # one copy of [slow | fast]
 
     def submit(self, host_clips: torch.Tensor, params: Sequence[ClipParams]) -> int:
         if tuple(host_clips.shape) != (self.batch,) + self.clip_shape or host_clips.dtype != torch.uint8:
@@ -88,6 +118,7 @@ class StagedPreprocess:
         slot = self.slots[self._n % len(self.slots)]
         if self.in_place:
             return self._submit_in_place(slot, host_clips, params)
+        slot.host_clips = host_clips  # stays referenced while the copy queued below may still read it
         with torch.cuda.stream(self.s_in):
             if slot.used:
                 self.s_in.wait_event(slot.kernel_done)  # the kernel that read this slot has finished
@@ -107,8 +138,7 @@ class StagedPreprocess:
             slot.in_ready.record(self.s_in)
         with torch.cuda.stream(self.s_run):
             self.s_run.wait_event(slot.in_ready)
-            if slot.used and self.host_out:
-                self.s_run.wait_event(slot.out_ready)  # the previous result has left the slot
+            self._wait_for_consumer(slot)
             # the clips arrived through a copy on another stream (event-ordered): nothing the previous
             # kernel on s_run did can have produced them
             prepared = self.t.prepare_batch(slot.dev_in, params, out=slot.raw_out, clips_ready=True)
@@ -117,8 +147,7 @@ class StagedPreprocess:
         if self.host_out:
             with torch.cuda.stream(self.s_out):
                 self.s_out.wait_event(slot.kernel_done)
-                for h, r in zip(slot.host_out, slot.raw_out):
-                    h.copy_(r, non_blocking=True)
+                slot.host_flat.copy_(slot.flat_out, non_blocking=True)  # [slow | fast] in one copy
                 slot.out_ready.record(self.s_out)
         slot.used = True
         ticket = self._n
@@ -134,9 +163,9 @@ class StagedPreprocess:
             fh, _fw = _lib.source_footprint(h, w, p.oh, p.ow, p.top, p.left, self.t.crop_size)
             rows += fh
         self.h2d_bytes = c * self.t.num_frames * rows * w
+        slot.host_clips = host_clips
         with torch.cuda.stream(self.s_run):
-            if slot.used and self.host_out:
-                self.s_run.wait_event(slot.out_ready)  # the previous result has left the slot
+            self._wait_for_consumer(slot)
             prepared = self.t.prepare_batch(host_clips, params, out=slot.raw_out, clips_ready=True,
                                             max_ctas=self.max_ctas, device=self.device)
             prepared.launch_raw(self.s_run.cuda_stream)
@@ -148,25 +177,53 @@ class StagedPreprocess:
         if self.host_out:
             with torch.cuda.stream(self.s_out):
                 self.s_out.wait_event(slot.kernel_done)
-                for h_, r in zip(slot.host_out, slot.raw_out):
-                    h_.copy_(r, non_blocking=True)
+                slot.host_flat.copy_(slot.flat_out, non_blocking=True)  # [slow | fast] in one copy
                 slot.out_ready.record(self.s_out)
         slot.used = True
         ticket = self._n
         self._n += 1
         return ticket
 
+    def _wait_for_consumer(self, slot: _Slot) -> None:
+        """Called on s_run before a slot's outputs are overwritten."""
+        if not slot.used:
+            return
+        if self.host_out:
+            self.s_run.wait_event(slot.out_ready)  # the previous result has left the slot
+        elif slot.released is not None:
+            self.s_run.wait_event(slot.released)  # whoever took result() has finished reading raw_out
+            slot.released = None
+        elif slot.consumer_stream is not None:
+            self.s_run.wait_stream(slot.consumer_stream)  # everything the consumer has enqueued there so far
+            slot.consumer_stream = None
+
     def result(self, ticket: int) -> List[torch.Tensor]:
         """Block until batch ``ticket`` is complete.  Returns the pinned host tensors (``host_out=True``,
-        raw ``N x T x S x S x C`` order) or the device tensors as ``[slow, fast]`` logical views."""
+        raw ``N x T x S x S x C`` order) or the device tensors as ``[slow, fast]`` logical views.
+
+        Device views stay valid until the slot is reused (``depth`` submits later).  Work the caller
+        enqueues on the stream that is current NOW is waited for automatically before that reuse; a
+        consumer on another stream calls ``release(ticket)`` when it has enqueued its last read."""
         if ticket < self._n - len(self.slots) or ticket >= self._n:
             raise ValueError("ticket is no longer (or not yet) resident in a slot")
         slot = self.slots[ticket % len(self.slots)]
         if self.host_out:
             slot.out_ready.synchronize()
+            slot.host_clips = None
             return slot.host_out
         slot.kernel_done.synchronize()
+        slot.host_clips = None
+        slot.consumer_stream = torch.cuda.current_stream(self.device)
         return [self.t._logical(r) for r in slot.raw_out]
+
+    def release(self, ticket: int, stream: Optional[torch.cuda.Stream] = None) -> None:
+        """Declare that everything enqueued so far on ``stream`` (default: the current stream) is all
+        that will ever read the device tensors of ``ticket``."""
+        slot = self.slots[ticket % len(self.slots)]
+        ev = torch.cuda.Event()
+        ev.record(stream if stream is not None else torch.cuda.current_stream(self.device))
+        slot.released = ev
+        slot.consumer_stream = None
 
     def drain(self) -> None:
         for s in (self.s_in, self.s_run, self.s_out):

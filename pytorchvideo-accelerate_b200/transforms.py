@@ -226,6 +226,10 @@ class GpuClipTransform:
             if v.device != src_device:
                 raise ValueError("all clips of a batch must live on one device")
             if not v.is_contiguous():
+                if not v.is_cuda:
+                    # .contiguous() would hand the kernel a fresh PAGEABLE copy, which it cannot read
+                    raise ValueError("host clips that are read in place must be contiguous (got a strided view); "
+                                     "make them contiguous before pinning")
                 v = v.contiguous()
             if v.dtype != clip_list[0].dtype:
                 raise TypeError("all clips of a batch must share one dtype")
@@ -472,13 +476,22 @@ class GpuPreprocess:
             batch["video"] = out if self.t.is_slowfast else out[0]
             del batch[PARAMS_KEY]
             return batch
-        if (self.upload_selected_frames and isinstance(video, torch.Tensor) and not video.is_cuda
-                and video.dtype == torch.uint8 and video.is_contiguous()):
+        raw_dma = (self.upload_selected_frames and isinstance(video, torch.Tensor) and not video.is_cuda
+                   and video.dtype == torch.uint8 and video.is_contiguous())
+        if raw_dma:
             clips = self._upload_selected(video, dev)
         elif isinstance(video, torch.Tensor):
             clips = video.to(dev, non_blocking=True)
         else:
             clips = [v.to(dev, non_blocking=True) for v in video]
+        if raw_dma:
+            # The strided copies were queued through the C ABI, behind torch's back: its host allocator
+            # does not know that the pinned batch is still being read and would recycle the block as
+            # soon as the batch dict drops it.  Keep the batch until the copies have run.
+            self._in_flight = [(e, v) for e, v in self._in_flight if not e.query()]
+            copied = torch.cuda.Event()
+            copied.record(torch.cuda.current_stream(dev))
+            self._in_flight.append((copied, video))
         out = self.t.prepare_batch(clips, params, clips_ready=from_host).launch()
         batch["video"] = out if self.t.is_slowfast else out[0]
         del batch[PARAMS_KEY]

@@ -163,3 +163,31 @@ def test_environment_cannot_switch_off_stores_or_fences(cuda_device):
         out = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, check=True).stdout
         digests.append(out.strip().splitlines()[-1])
     assert digests[0] == digests[1] == digests[2]
+
+
+@pytest.mark.parametrize("kernel", ["generic", "tiled"])
+def test_clip_at_the_edges_of_its_allocation(kernel, cuda_device):
+    """The band copies of the tiled kernel start at the 16-byte granule of their first byte and end at
+    the granule of their last one: only granules that hold at least one byte of the clip are read.
+    Allocation (and mapping) boundaries are aligned far more coarsely, so a clip that starts at the
+    first byte or ends at the last byte of a cudaMalloc'ed block is safe.  Exercise both, with corner
+    crop windows whose taps touch the clip's first and last bytes."""
+    kw = full_kwargs(dict(num_frames=4, slowfast_alpha=2, crop_size=128, min_short_side_scale=128))
+    t = pva_b200.make_transform(**kw, out_dtype=torch.float32, norm_mode="exact", kernel=kernel)
+    shape = (3, 6, 130, 171)
+    clip = synth_clip(shape, 4242)
+    n = clip.numel()
+    block_bytes = 32 << 20  # a whole number of 2 MiB pages: the caching allocator hands out the cudaMalloc block itself
+    oh, ow = pipeline.resized_hw(130, 171, 128)
+    windows = [ClipParams(128, oh, ow, 0, 0, False), ClipParams(128, oh, ow, oh - 128, ow - 128, True)]
+    for where in ("start", "end"):
+        block = torch.empty(block_bytes, dtype=torch.uint8, device="cuda")
+        off = 0 if where == "start" else block_bytes - n
+        dev = block[off:off + n].view(shape)
+        dev.copy_(clip)
+        for p in windows:
+            slow, fast = t.run_batch([dev], [p])
+            torch.cuda.synchronize()
+            rs, rf = oracle_clip(clip, p, kw)
+            assert np.array_equal(fast[0].cpu().numpy(), rf) and np.array_equal(slow[0].cpu().numpy(), rs)
+        del dev, block

@@ -221,11 +221,12 @@ def test_full_size_train_batch_properties(kernel, cuda_device):
     assert torch.equal(fast_f, fast.flip(-1))
     _, single = t.run_batch(clips[3:4], params[3:4])
     assert torch.equal(single[0], fast[3])
-    # spot-check two clips on every element against the oracle
-    for i in (0, 5):
-        p = params[i]
+    # every clip, both pathways, every element against the oracle (the benchmark's mode: AFFINE, fp16,
+    # channels-last)
+    for i, p in enumerate(params):
         rs, rf = c_oracle_explicit(clips[i].cpu(), (p.size, p.top, p.left, p.flip), kw)
-        assert np.abs(fast[i].float().cpu().numpy() - rf).max() <= FP16_TOL
+        assert np.abs(fast[i].float().cpu().numpy() - rf).max() <= FP16_TOL, i
+        assert np.abs(slow[i].float().cpu().numpy() - rs).max() <= FP16_TOL, i
 
 
 def test_dict_contract_and_seeded_draws(cuda_device):
@@ -293,3 +294,79 @@ def test_float32_frames_like_the_decoder_hands_over(cuda_device):
         t16 = pva_b200.make_transform(**kw)
         for o, r in zip(t16.explicit(clip.cuda(), params_from_draws(draws, 128, 172)), ref):
             assert np.abs(o.float().cpu().numpy() - r.numpy()).max() <= FP16_TOL
+
+
+def bench_batch(workload, rank=0):
+    """The exact clips and draws bench.py's device-resident region uses for its first buffer set."""
+    import bench
+
+    wl = bench.WORKLOADS[workload]
+    B, shape, kw = wl["batch"], wl["shape"], wl["kwargs"]
+    t = pva_b200.make_transform(**kw)
+    gen = torch.Generator().manual_seed(1234 + rank)
+    torch.manual_seed(42 + rank)
+    clips = torch.randint(0, 256, (B,) + tuple(shape), dtype=torch.uint8, generator=gen)
+    params = [t.sample_params(shape[2], shape[3]) for _ in range(B)]
+    return t, full_kwargs(kw), clips, params
+
+
+def test_in_place_pinned_read_at_full_size_is_bit_equal_and_within_tolerance(cuda_device):
+    """The e2e default of bench.py: StagedPreprocess(read_in_place=True, max_ctas=8) on the headline
+    batch (8 x 3x64x256x340, the benchmark's seeds).  The kernel reads the pinned host batch over PCIe
+    on 8 CTAs; the result must equal the device-resident launch bit for bit and the oracle within 1e-3."""
+    t, kw, clips, params = bench_batch("slowfast_train_b8")
+    pinned = clips.pin_memory()
+    staged = pva_b200.StagedPreprocess(t, 8, tuple(clips.shape[1:]), cuda_device, depth=3, host_out=True,
+                                       read_in_place=True, max_ctas=8)
+    tickets = [staged.submit(pinned, params) for _ in range(2)]
+    host_slow, host_fast = staged.result(tickets[1])
+    assert _lib.last_launch_info()["grid"] == 8
+    slow, fast = t.run_batch(clips.cuda(), params)
+    torch.cuda.synchronize()
+    assert _lib.last_launch_info()["grid"] > 8
+    assert torch.equal(host_fast.permute(0, 4, 1, 2, 3), fast.cpu())
+    assert torch.equal(host_slow.permute(0, 4, 1, 2, 3), slow.cpu())
+    for i in (1, 6):
+        p = params[i]
+        rs, rf = c_oracle_explicit(clips[i], (p.size, p.top, p.left, p.flip), kw)
+        assert np.abs(host_fast[i].permute(3, 0, 1, 2).float().numpy() - rf).max() <= FP16_TOL
+        assert np.abs(host_slow[i].permute(3, 0, 1, 2).float().numpy() - rs).max() <= FP16_TOL
+    staged.drain()
+
+
+def test_config4_single_pathway_batch_64_at_its_own_shape(cuda_device):
+    """BASELINE.json configs[3]: 64 clips per launch, 16 frames, crop 224, single pathway, train draws --
+    the benchmark's own clips and seeds; every clip, every element against the oracle."""
+    t, kw, clips, params = bench_batch("single_pathway_b64")
+    (fast,) = t.run_batch(clips.cuda(), params)
+    torch.cuda.synchronize()
+    info = _lib.last_launch_info()
+    assert info["kernel"] == 2 and info["launches"] == 1
+    assert fast.shape == (64, 3, 16, 224, 224) and fast.dtype == torch.float16
+    fast = fast.float().cpu().numpy()
+    worst = 0.0
+    for i, p in enumerate(params):
+        (rf,) = c_oracle_explicit(clips[i], (p.size, p.top, p.left, p.flip), kw)
+        worst = max(worst, float(np.abs(fast[i] - rf).max()))
+    assert worst <= FP16_TOL
+
+
+@pytest.mark.parametrize("kernel", KERNELS)
+def test_fp16_headroom_on_bright_clips(kernel, cuda_device):
+    """Values in [2, 4) -- pixels >= 230 after Normalize(0.45, 0.225) -- have an fp16 half-ulp of 9.766e-4,
+    so the production mode has 1e-3 - 9.766e-4 = 2.3e-5 to spend on its fp32 internals.  AFFINE spends
+    < 4e-6 of it.  This test fails if someone widens that: max|err| must stay <= 9.8e-4 on clips made of
+    bright pixels only (255s, and random 230..255), resized so that interpolated values spread."""
+    kw = full_kwargs(dict(training=True))
+    t = pva_b200.make_transform(**kw, kernel=kernel)
+    g = torch.Generator().manual_seed(77)
+    bright = torch.randint(230, 256, (3, 64, 256, 340), dtype=torch.uint8, generator=g)
+    white = torch.full((3, 64, 256, 340), 255, dtype=torch.uint8)
+    worst = 0.0
+    for clip, draws in ((bright, (313, 21, 40, True)), (bright, (256, 0, 42, False)), (white, (288, 5, 7, False))):
+        p = params_from_draws(draws, 256, 340)
+        slow, fast = supported(kernel, lambda: t.run_batch(clip[None].cuda(), [p]))
+        rs, rf = c_oracle_explicit(clip, draws, kw)
+        worst = max(worst, float(np.abs(fast[0].float().cpu().numpy() - rf).max()),
+                    float(np.abs(slow[0].float().cpu().numpy() - rs).max()))
+    assert worst <= 9.8e-4, worst

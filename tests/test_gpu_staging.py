@@ -138,3 +138,55 @@ def test_back_to_back_launches_into_the_same_outputs_keep_stream_order(cuda_devi
         torch.cuda.synchronize()
         got = prepared[last].outputs
         assert all(torch.equal(g, w) for g, w in zip(got, want[last])), (rounds, last)
+
+
+def test_device_results_are_not_overwritten_under_a_running_consumer(cuda_device):
+    """host_out=False hands out views of the slot's device buffers.  A consumer that is still reading
+    them on the current stream when the slot comes round again must be waited for: here the consumer
+    is a long chain of kernels enqueued right after result(), and the slot is resubmitted at once."""
+    kw = dict(min_short_side_scale=128, max_short_side_scale=160, crop_size=128, num_frames=8, training=True)
+    t = pva_b200.make_transform(**kw)
+    shape = (3, 16, 128, 172)
+    staged = pva_b200.StagedPreprocess(t, 4, shape, cuda_device, depth=2, host_out=False)
+    torch.manual_seed(8)
+    batches = []
+    for b in range(4):
+        clips = torch.stack([synth_clip(shape, 500 * b + i) for i in range(4)]).pin_memory()
+        batches.append((clips, [t.sample_params(128, 172) for _ in range(4)]))
+    want = [[o.clone() for o in t.run_batch(c.cuda(), p)] for c, p in batches]
+    torch.cuda.synchronize()
+    spin = torch.empty(64 << 20, dtype=torch.float32, device=cuda_device)
+    t0 = staged.submit(*batches[0])
+    slow, fast = staged.result(t0)
+    for _ in range(30):  # ~ms of queued work on the current stream ahead of the consumer's read
+        spin.add_(1.0)
+    late_copy = [slow.clone(), fast.clone()]  # the consumer's read, queued behind the spinning
+    staged.submit(*batches[1])
+    staged.submit(*batches[2])  # depth 2: this one reuses ticket 0's slot
+    torch.cuda.synchronize()
+    assert torch.equal(late_copy[0], want[0][0]) and torch.equal(late_copy[1], want[0][1])
+    # an explicit release on a side stream is honoured the same way
+    side = torch.cuda.Stream(cuda_device)
+    t3 = staged.submit(*batches[3])  # reuses ticket 1's slot
+    slow3, fast3 = staged.result(t3)
+    with torch.cuda.stream(side):
+        for _ in range(30):
+            spin.add_(1.0)
+        got = fast3.clone()
+        staged.release(t3, side)
+    staged.submit(*batches[0])
+    staged.submit(*batches[1])  # reuses ticket 3's slot: must wait for `side`
+    torch.cuda.synchronize()
+    assert torch.equal(got, want[3][1])
+    staged.drain()
+
+
+def test_strided_pinned_clip_is_rejected_not_copied(cuda_device):
+    """A non-contiguous pinned clip cannot be read in place, and making it contiguous would silently
+    produce a pageable copy the kernel cannot reach: ValueError instead."""
+    t = pva_b200.make_transform(min_short_side_scale=64, crop_size=64, num_frames=4, slowfast_alpha=2)
+    base = synth_clip((3, 8, 64, 160), 1).pin_memory()
+    view = base[:, :, :, :80]
+    assert view.is_pinned() and not view.is_contiguous()
+    with pytest.raises(ValueError, match="contiguous"):
+        t.prepare_batch([view], [t.sample_params(64, 80)], device=cuda_device)
