@@ -456,7 +456,10 @@ def run_b200_arm(args):
     for s in range(n_sets):
         clips = torch.randint(0, 256, (B,) + tuple(shape), dtype=torch.uint8, generator=gen).to(dev)
         params = [t.sample_params(shape[2], shape[3]) for _ in range(B)]
-        sets.append(t.prepare_batch(clips, params, clips_ready=True))  # resident and complete before the timed region
+        # resident and complete before the timed region; every set has its own outputs, so consecutive
+        # launches never share an output buffer (what a prefetching input pipeline's ring looks like)
+        sets.append(t.prepare_batch(clips, params, out=t.alloc_outputs(B, dev), clips_ready=True,
+                                    outputs_disjoint=not args.serialize_stores))
         b = 0
         for p in params:
             fh, fw = _lib.source_footprint(shape[2], shape[3], p.oh, p.ow, p.top, p.left, crop)
@@ -611,7 +614,8 @@ def run_b200_arm(args):
         "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic", "config": config,
         "impl_detail": {"out": "fp16 CTHW (the reference's memory order)" if args.planar else "fp16 THWC (channels_last_3d)",
-                        "norm_mode": args.norm_mode, "launch": info, "cuda_graph": bool(args.graph),
+                        "norm_mode": args.norm_mode, "launch": info,
+                        "flags": "PVA_FLAG_CLIPS_READY" + ("" if args.serialize_stores else " | PVA_FLAG_OUTPUTS_DISJOINT"), "cuda_graph": bool(args.graph),
                         "pinned_cores": pinned_cores},
         "roofline": roofline, "launch_us_isolated": launch_us_isolated, "host_us_per_call": host_us,
         "e2e": e2e, "gpu_launches": args.steps * info["launches"], "clocks": clocks,
@@ -783,6 +787,8 @@ def main():
                     help="e2e H2D leg: whole clips, only the selected frames, or auto (see run_e2e)")
     ap.add_argument("--upload-all-frames", action="store_true",
                     help="e2e: copy whole clips to the device instead of only the frames the transform selects")
+    ap.add_argument("--serialize-stores", action="store_true",
+                    help="do not set PVA_FLAG_OUTPUTS_DISJOINT: every launch waits for the previous one before its first store")
     ap.add_argument("--planar", action="store_true",
                     help="write the reference's contiguous C x T x S x S order instead of channels-last (experiments)")
     ap.add_argument("--batch", type=int, default=0, help="override the workload's batch (experiments)")

@@ -78,6 +78,16 @@ typedef enum PvaSrcType { PVA_SRC_U8 = 0, PVA_SRC_F32 = 1 } PvaSrcType;
  * freely; that ordering is always kept).  Without the flag a launch waits for the previous
  * kernel before it touches memory at all. */
 #define PVA_FLAG_CLIPS_READY 1
+/* PVA_FLAG_OUTPUTS_DISJOINT (only honoured together with PVA_FLAG_CLIPS_READY): the caller asserts
+ * that the previous kernel of this stream neither reads nor writes any byte of this call's fast_out /
+ * slow_out -- e.g. consecutive batches go to different buffers of a ring, as a prefetching data
+ * pipeline has them anyway.  The launch then does not wait for the previous kernel at all before it
+ * stores: it fills the SMs the previous launch's slowest blocks have not reached yet, and the two
+ * overlap completely.  Stream order as seen from outside is unchanged (a block of this launch does
+ * not exit before the previous kernel has completed, so whatever follows on the stream still sees
+ * both finished).  Do NOT set it when the same output buffer is handed to consecutive calls, or when
+ * outputs come fresh from a caching allocator that may recycle the previous call's block. */
+#define PVA_FLAG_OUTPUTS_DISJOINT 2
 /* Limits: 1..4 channels; n_fast, n_slow <= 128; t_in <= 65535; any h, w, crop.  More than 128 clips
  * or 8 distinct frame_idx tables per call are handled with several launches.  The tiled kernel takes
  * 3-channel uint8 clips, either layout and crops up to 2048; everything else runs on the

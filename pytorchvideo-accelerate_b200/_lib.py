@@ -25,6 +25,7 @@ PVA_NORM_EXACT, PVA_NORM_AFFINE = 0, 1
 PVA_KERNEL_AUTO, PVA_KERNEL_GENERIC, PVA_KERNEL_TILED = 0, 1, 2
 PVA_SRC_U8, PVA_SRC_F32 = 0, 1
 PVA_FLAG_CLIPS_READY = 1
+PVA_FLAG_OUTPUTS_DISJOINT = 2
 
 EXPORTED_SYMBOLS = (
     "pva_preprocess",

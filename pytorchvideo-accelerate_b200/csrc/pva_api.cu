@@ -147,6 +147,8 @@ int pva_preprocess(const PvaClipDesc* clips, int32_t n_clips, const PvaPlan* pla
     if (plan->src_type != PVA_SRC_U8 && plan->src_type != PVA_SRC_F32)
         return fail(PVA_ERR_INVALID_ARGUMENT, "src_type=%d is not a PvaSrcType", plan->src_type);
     if (plan->max_ctas < 0) return fail(PVA_ERR_INVALID_ARGUMENT, "max_ctas=%d is negative", plan->max_ctas);
+    if (plan->flags & ~(PVA_FLAG_CLIPS_READY | PVA_FLAG_OUTPUTS_DISJOINT))
+        return fail(PVA_ERR_INVALID_ARGUMENT, "flags=0x%x has bits that are not PVA_FLAG_*", plan->flags);
     if ((plan->n_slow == 0) != (slow_out == nullptr))
         return fail(PVA_ERR_INVALID_ARGUMENT, "slow_out must be NULL exactly when n_slow == 0 (n_slow=%d)",
                     plan->n_slow);
@@ -189,6 +191,7 @@ int pva_preprocess(const PvaClipDesc* clips, int32_t n_clips, const PvaPlan* pla
     kp.crop = crop;
     kp.src_f32 = plan->src_type == PVA_SRC_F32 ? 1 : 0;
     kp.clips_ready = (plan->flags & PVA_FLAG_CLIPS_READY) ? 1 : 0;
+    kp.outputs_disjoint = (plan->flags & PVA_FLAG_OUTPUTS_DISJOINT) ? 1 : 0;
     kp.max_ctas = plan->max_ctas;
     kp.fast_clip_elems = (long long)C * plan->n_fast * crop * crop;
     kp.slow_clip_elems = (long long)C * plan->n_slow * crop * crop;

@@ -35,6 +35,7 @@ struct KParams {
     int n_clips, C, n_fast, n_slow, crop;
     int src_f32;        // source clips are float32 (0..255 valued) instead of uint8: generic kernel only
     int clips_ready;    // PVA_FLAG_CLIPS_READY: reading the clips need not wait for the previous kernel
+    int outputs_disjoint;  // PVA_FLAG_OUTPUTS_DISJOINT: the previous kernel does not touch this launch's outputs
     int max_ctas;       // PvaPlan.max_ctas: grid cap of the tiled kernel (0 = one CTA per SM)
     long long fast_clip_elems;  // C * n_fast * crop * crop
     long long slow_clip_elems;

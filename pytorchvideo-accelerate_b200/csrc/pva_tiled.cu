@@ -93,7 +93,9 @@ struct TileGeom {
     int bulk_store;    // 1: cp.async.bulk stores are legal (alignment), 0: plain stores
     int total_tiles;
     int off_ytab, off_in, off_out, off_lut;
-    int pdl;         // programmatic dependent launch: 0 off, 1 wait before the first store, 2 wait at the start
+    int pdl;         // programmatic dependent launch: 0 off, 1 wait before the first store, 2 wait at the start,
+                     // 3 wait only before the CTA exits (PVA_FLAG_OUTPUTS_DISJOINT)
+    int tile0_first; // the producer lets a CTA's first tile land before it requests the next ones
     int load_rows;   // 1: column-cropped source rows through 128-bit cp.async, one row per producer lane;
                      // 0: one cp.async.bulk per plane over the full-width row band
     int l2hint;      // bit 0: loads evict_first, bit 1: stores evict_first
@@ -105,6 +107,8 @@ struct TileGeom {
     // column-cropped loads (kColCrop): per clip, the staged row pitch in bytes (box width) and the
     // 4-row groups a box holds; see the comment above tensor_load_4d
     int colcrop;
+    // experiments only: per-CTA time stamps (8 x uint64 %globaltimer ns per CTA) of this launch, or null
+    unsigned long long* trace;
     uint16_t cc_bw[kMaxCropClips];
     uint16_t cc_ng[kMaxCropClips];
 };
@@ -209,6 +213,17 @@ __device__ __forceinline__ uint32_t lds8(uint32_t addr) {
     asm volatile("ld.shared.u8 %0, [%1];" : "=r"(v) : "r"(addr));
     return v;
 }
+
+__device__ __forceinline__ unsigned long long global_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+// Experiments build: stamp slot `slot` of this CTA's trace record (first writer wins when once == true).
+#define PVA_TRACE(slot)                                                             \
+    do {                                                                            \
+        if (kExperiments && tg.trace) tg.trace[(size_t)blockIdx.x * 8 + (slot)] = global_ns(); \
+    } while (0)
 
 // Source row / column range of a tile, from the same tap formula the consumers use.
 __device__ __forceinline__ void src_range(float scale, int first_dst, int last_dst, int in_size, int& a, int& n) {
@@ -330,6 +345,7 @@ __global__ void __launch_bounds__(kBlockThreads, 1)
     __shared__ __align__(8) unsigned long long s_empty[kMaxStages];
 
     const int tid = threadIdx.x;
+    if (tid == 0) PVA_TRACE(0);  // kernel entry
     const int crop = p.crop;
     const int n_stages = tg.stages;
     // contiguous tile range of this CTA (tiles are ordered clip, frame, band)
@@ -358,11 +374,17 @@ __global__ void __launch_bounds__(kBlockThreads, 1)
         // one, and it never writes clip bytes -- but nothing may be WRITTEN before the previous
         // kernel has completed (the caller may be reusing the output buffers): the threads that
         // issue stores wait right before their first store, everybody else never has to.
+        //
+        // pdl == 3 (the caller vouches that the previous kernel neither reads nor writes this launch's
+        // outputs): nothing is waited for before the stores either, so the launch overlaps the previous
+        // one's tail completely.  One thread per CTA still executes the wait before the CTA exits, which
+        // keeps completion transitive: this grid cannot complete before its predecessor has.
         asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
         if (!tg.bulk_store || tg.pdl == 2) asm volatile("griddepcontrol.wait;" ::: "memory");
     }
 
     const uint32_t in_base = smem_u32(smem + tg.off_in);
+    if (tid == 0) PVA_TRACE(1);  // set-up done
 
     if (tid >= kConsumerThreads) {
         // ------------------------------ producer warp ------------------------------
@@ -450,9 +472,15 @@ __global__ void __launch_bounds__(kBlockThreads, 1)
                     else bulk_load(st_base + (uint32_t)lane * tg.plane_stride, g0 - sh, bytes, bar);
                 }
             }
+            // At the start of a launch every SM asks for its whole ring at once (148 x 3 tiles = 13 MB)
+            // and a CTA's first tile used to land only after ~3 us, behind everybody's second and third.
+            // Let tile 0 land before asking for more: it arrives in about half the time and the first
+            // consumer group starts that much earlier; steady state is unaffected.
+            if (tg.tile0_first && t == t_begin) mbar_wait(bar, 0u);
             if (++s == n_stages) s = 0, ph ^= 1u;
         }
         if (load_rows) asm volatile("cp.async.wait_all;" ::: "memory");  // no copy may outlive the CTA
+        if (lane == 0) PVA_TRACE(7);  // all loads issued
         return;
     }
 
@@ -469,7 +497,6 @@ __global__ void __launch_bounds__(kBlockThreads, 1)
     const int gx = (crop + kPx - 1) / kPx;
     const bool in_strip = strip < tg.n_strips;
     const int bar_strip = 1 + group * tg.n_strips + strip;  // named barrier of this strip (1..8)
-    const int bar_group = 15 - group;                       // named barrier of this consumer group
     const bool active_col = g_col < gx && in_strip;
     const bool full_group = (kPx * g_col + kPx) <= crop && (crop & 3) == 0;  // vector staging stores need crop % 4 == 0
     const int strip_threads = tg.tps;
@@ -504,8 +531,11 @@ __global__ void __launch_bounds__(kBlockThreads, 1)
         const int band = rem - k * tg.bands;
 
         if (clip_i != cur_clip) {
-            // every strip of the group must have left the previous clip before its row table is rebuilt
-            named_bar(bar_group, group_threads);
+            // A strip rebuilds only ITS OWN rows of the row table (the rows it computes in every band),
+            // so a clip change needs no barrier beyond the strip's own: its threads all passed the
+            // strip barrier of the previous tile's store, i.e. none of them still reads the old rows.
+            // (A group-wide barrier here cost the CTAs that cross a clip boundary ~3 us: it lines up
+            // strips that otherwise drift apart by up to a tile, which is what keeps the stores flowing.)
             cur_clip = clip_i;
             const ClipGeom& g = p.clips[clip_i];
             src = g.src, W = g.w, H = g.h, T_in = g.t_in, idx_row = g.idx_row;
@@ -522,7 +552,9 @@ __global__ void __launch_bounds__(kBlockThreads, 1)
                 src_range(g.sx, g.left, g.left + crop - 1, g.w, c0, n0);
                 cc_ca = (uint32_t)c0;
             }
-            for (int y = gtid; y < crop; y += group_threads) {
+            for (int i = g_col; i < tg.bands * tg.rps && in_strip; i += strip_threads) {
+                const int y = (i / tg.rps) * tg.R + strip * tg.rps + (i % tg.rps);
+                if (y >= crop) continue;
                 int y0, y1;
                 float l0, l1;
                 bilinear_taps(g.sy, g.top + y, g.h, y0, y1, l0, l1);
@@ -557,7 +589,7 @@ __global__ void __launch_bounds__(kBlockThreads, 1)
                 sel0 |= (uint32_t)((x0v[i] - wc) & 7) << (4 * i);
                 sel1 |= (uint32_t)((x1v[i] - wc) & 7) << (4 * i);
             }
-            named_bar(bar_group, group_threads);
+            if (in_strip) named_bar(bar_strip, strip_threads);  // the strip's rows of the table are complete
         }
 
         const int yb = band * tg.R;
@@ -575,6 +607,7 @@ __global__ void __launch_bounds__(kBlockThreads, 1)
 
         // every thread polls: measured faster than one poller per warp + __syncwarp (43.4 vs 46.0 us)
         mbar_wait(smem_u32(&s_full[2 * s + group]), ph);
+        if (tid == 0 && t == t_begin) PVA_TRACE(2);  // first tile landed
 
         if (active_col && rows > 0 && !(dbg & 4)) {
             // staged address of (plane c, source row r, window start) = rowbase[c] + r * pitch
@@ -591,7 +624,13 @@ __global__ void __launch_bounds__(kBlockThreads, 1)
                     rowbase[c] = in_base + (uint32_t)s * tg.stage_bytes + (uint32_t)c * ng * bw -
                                  (uint32_t)(ra >> 2) * bw + (uint32_t)woff;
             } else {
-                const int ra = ytab[yb].x;  // first source row staged for this tile
+                int ra;  // first source row staged for this tile (row yb of the table belongs to strip 0)
+                {
+                    const ClipGeom& g = p.clips[clip_i];
+                    int rb;
+                    float l0, l1;
+                    bilinear_taps(g.sy, g.top + yb, g.h, ra, rb, l0, l1);
+                }
                 const int t_src = p.frame_idx[idx_row][k];
 #pragma unroll
                 for (int c = 0; c < 3; ++c) {
@@ -727,10 +766,12 @@ __global__ void __launch_bounds__(kBlockThreads, 1)
                 }
                 named_bar(bar_strip, strip_threads);
                 if (g_col == 0 && rows > 0 && !(dbg & 1)) {
+                    if (tid == 0 && t == t_begin) PVA_TRACE(3);  // first strip computed, about to store
                     if (!may_store) {
                         asm volatile("griddepcontrol.wait;" ::: "memory");
                         may_store = true;
                     }
+                    if (tid == 0 && t == t_begin) PVA_TRACE(4);  // previous kernel complete (PDL wait returned)
                     const uint32_t ssrc = smem_u32(stage_out);
                     if (kPlanar) {
                         // one contiguous range per channel plane: rows x crop elements
@@ -800,7 +841,10 @@ __global__ void __launch_bounds__(kBlockThreads, 1)
         }
     }
     // the staging buffers must outlive the stores' reads; the writes themselves complete with the kernel
+    if (tid == 0) PVA_TRACE(5);  // last tile of group 0 handed to the store engine
+    if (tg.pdl == 3 && tid == 0) asm volatile("griddepcontrol.wait;" ::: "memory");  // completion stays transitive
     if (tg.bulk_store && g_col == 0 && in_strip) bulk_wait_read_all();
+    if (tid == 0) PVA_TRACE(6);  // staging drained: CTA about to exit
 }
 
 int round_up(int v, int m) { return (v + m - 1) / m * m; }
@@ -1010,6 +1054,7 @@ bool plan_tiles(const KParams& p, int out_dtype, int layout, TileGeom* tg, const
         tg->na_uniform = (p.na[0] == p.na[1] && p.na[1] == p.na[2]) ? 1 : 0;
         tg->debug = PVA_KNOB("DEBUG", 0);
         tg->colcrop = colcrop ? 1 : 0;
+        tg->trace = nullptr;
         return true;
     }
     *why = "tile does not fit shared memory (source rows too wide for this scale)";
@@ -1149,13 +1194,30 @@ cudaError_t launch_tiled(const KParams& p, int out_dtype, int layout, int norm, 
         fastx = fastx && (g.w <= g.ow) && (g.w % 4 == 0) && ((uintptr_t)g.src % 4 == 0);
     }
     static_cast<TiledArgs&>(a).p = p;
-    // 1: wait for the previous kernel only before the first store (PVA_FLAG_CLIPS_READY); 2: wait
-    // before touching memory at all.  The ordering of the stores is never negotiable.
-    a.g.pdl = p.clips_ready ? 1 : 2;
+    // 2: wait for the previous kernel before touching memory at all; 1 (PVA_FLAG_CLIPS_READY): only
+    // before the first store; 3 (+ PVA_FLAG_OUTPUTS_DISJOINT): only before the CTA exits.  Only the
+    // caller's explicit flags ever relax the ordering.
+    a.g.pdl = p.clips_ready ? (p.outputs_disjoint ? 3 : 1) : 2;
 #ifdef PVA_EXPERIMENTS
     a.g.pdl = knob_env("PVA_TILED_PDL", a.g.pdl);  // 0 = no programmatic dependent launch at all
 #endif
+    a.g.tile0_first = PVA_KNOB("TILE0_FIRST", 1);
     a.g.l2hint = PVA_KNOB("L2HINT", 3);  // clip bytes are read once, outputs are consumed later: stream both
+#ifdef PVA_EXPERIMENTS
+    {
+        // PVA_TILED_TRACE=<hex device address of a uint64 buffer, kMaxGrid * 8 entries per launch>,
+        // PVA_TILED_TRACE_SLOTS=<launch records the buffer holds>: consecutive launches fill
+        // consecutive records (scripts/trace_launch.py)
+        static std::atomic<unsigned> launch_no{0};
+        const char* tp = getenv("PVA_TILED_TRACE");
+        if (tp) {
+            const unsigned slots = (unsigned)knob_env("PVA_TILED_TRACE_SLOTS", 1);
+            const unsigned n = launch_no.fetch_add(1);
+            a.g.trace = reinterpret_cast<unsigned long long*>(strtoull(tp, nullptr, 16)) +
+                        (size_t)(n % slots) * kMaxGrid * 8;
+        }
+    }
+#endif
     int dev = 0;
     cudaGetDevice(&dev);
     const int sms = sm_count(dev);

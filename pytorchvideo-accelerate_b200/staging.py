@@ -141,7 +141,9 @@ class StagedPreprocess:
             self._wait_for_consumer(slot)
             # the clips arrived through a copy on another stream (event-ordered): nothing the previous
             # kernel on s_run did can have produced them
-            prepared = self.t.prepare_batch(slot.dev_in, params, out=slot.raw_out, clips_ready=True)
+            # consecutive kernels on s_run write different slots (depth >= 2): outputs are disjoint
+            prepared = self.t.prepare_batch(slot.dev_in, params, out=slot.raw_out, clips_ready=True,
+                                            outputs_disjoint=True)
             prepared.launch_raw(self.s_run.cuda_stream)
             slot.kernel_done.record(self.s_run)
         if self.host_out:
@@ -167,7 +169,7 @@ class StagedPreprocess:
         with torch.cuda.stream(self.s_run):
             self._wait_for_consumer(slot)
             prepared = self.t.prepare_batch(host_clips, params, out=slot.raw_out, clips_ready=True,
-                                            max_ctas=self.max_ctas, device=self.device)
+                                            max_ctas=self.max_ctas, device=self.device, outputs_disjoint=True)
             prepared.launch_raw(self.s_run.cuda_stream)
             slot.kernel_done = torch.cuda.Event()
             slot.kernel_done.record(self.s_run)

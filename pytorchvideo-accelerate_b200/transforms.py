@@ -144,9 +144,11 @@ class GpuClipTransform:
             tab = self._idx_cache[t_in] = _IdxTable(temporal_indices(t_in, self.num_frames))
         return tab
 
-    def _plan(self, src_dtype: torch.dtype = torch.uint8, clips_ready: bool = False, max_ctas: int = 0) -> _lib.PvaPlan:
+    def _plan(self, src_dtype: torch.dtype = torch.uint8, clips_ready: bool = False, max_ctas: int = 0,
+              outputs_disjoint: bool = False) -> _lib.PvaPlan:
         plan = _lib.PvaPlan()
-        plan.flags = _lib.PVA_FLAG_CLIPS_READY if clips_ready else 0
+        plan.flags = (_lib.PVA_FLAG_CLIPS_READY if clips_ready else 0) | (
+            _lib.PVA_FLAG_OUTPUTS_DISJOINT if outputs_disjoint else 0)
         plan.max_ctas = int(max_ctas)
         plan.channels = len(self.mean)
         plan.n_fast = self.num_frames
@@ -188,7 +190,8 @@ class GpuClipTransform:
 
     def prepare_batch(self, clips: Union[torch.Tensor, Sequence[torch.Tensor]], params: Sequence[ClipParams],
                       out: Optional[Sequence[torch.Tensor]] = None, clips_ready: bool = False,
-                      max_ctas: int = 0, device: Union[None, str, torch.device] = None) -> "PreparedBatch":
+                      max_ctas: int = 0, device: Union[None, str, torch.device] = None,
+                      outputs_disjoint: bool = False) -> "PreparedBatch":
         """Validate a batch and build its descriptor table once; ``.launch()`` then costs a
         single C call.  ``clips``: a ``B x C x T x H x W`` uint8 cuda tensor or a sequence of
         ``C x T x H x W`` uint8 cuda tensors (ragged shapes allowed).  ``out`` may supply raw
@@ -204,7 +207,14 @@ class GpuClipTransform:
         the clip bytes were complete before the previous kernel on the launch stream started (they
         came from a copy, or have been resident for a while) -- consecutive launches then overlap.
         Leave it off when a kernel enqueued right before this call produces the clips.
+
+        ``outputs_disjoint=True`` adds ``PVA_FLAG_OUTPUTS_DISJOINT``: the caller supplies ``out`` and
+        vouches that the previous kernel on the launch stream neither reads nor writes those buffers
+        (consecutive batches go to different slots of a ring).  The launch then overlaps the previous
+        one's tail completely.  Never combine it with outputs allocated per call.
         """
+        if outputs_disjoint and out is None:
+            raise ValueError("outputs_disjoint needs caller-owned output buffers (out=...)")
         clip_list = list(clips.unbind(0)) if isinstance(clips, torch.Tensor) and clips.dim() == 5 else list(clips)
         n = len(clip_list)
         if len(params) != n:
@@ -245,7 +255,8 @@ class GpuClipTransform:
             d.oh, d.ow, d.top, d.left, d.flip = p.oh, p.ow, p.top, p.left, int(p.flip)
         if out is None:
             out = self.alloc_outputs(n, device)
-        return PreparedBatch(self, descs, n, keep, list(out), device, clip_list[0].dtype, clips_ready, max_ctas)
+        return PreparedBatch(self, descs, n, keep, list(out), device, clip_list[0].dtype, clips_ready, max_ctas,
+                             outputs_disjoint)
 
     def run_batch(self, clips: Union[torch.Tensor, Sequence[torch.Tensor]], params: Sequence[ClipParams],
                   out: Optional[Sequence[torch.Tensor]] = None,
@@ -294,14 +305,14 @@ class PreparedBatch:
 
     def __init__(self, transform: GpuClipTransform, descs, n: int, clips: List[torch.Tensor],
                  out: List[torch.Tensor], device: torch.device, src_dtype: torch.dtype = torch.uint8,
-                 clips_ready: bool = False, max_ctas: int = 0):
+                 clips_ready: bool = False, max_ctas: int = 0, outputs_disjoint: bool = False):
         self.t = transform
         self.descs = descs
         self.n = n
         self.clips = clips
         self.raw_out = out
         self.device = device
-        self.plan = transform._plan(src_dtype, clips_ready, max_ctas)
+        self.plan = transform._plan(src_dtype, clips_ready, max_ctas, outputs_disjoint)
         self._plan_ref = ctypes.byref(self.plan)
         self.slow_raw, self.fast_raw = (out[0], out[1]) if transform.n_slow else (None, out[-1])
         self._fast_ptr = self.fast_raw.data_ptr()

@@ -42,7 +42,8 @@ def main():
     for _ in range(n_sets):
         clips = torch.randint(0, 256, (B,) + tuple(shape), dtype=torch.uint8, generator=gen).to(dev)
         params = [t.sample_params(shape[2], shape[3]) for _ in range(B)]
-        sets.append(t.prepare_batch(clips, params, clips_ready=True))
+        sets.append(t.prepare_batch(clips, params, out=t.alloc_outputs(B, dev), clips_ready=True,
+                                    outputs_disjoint=not os.environ.get("PVA_SERIALIZE_STORES")))
     stream = torch.cuda.current_stream(dev)
     raw = stream.cuda_stream
 

@@ -140,6 +140,47 @@ def test_back_to_back_launches_into_the_same_outputs_keep_stream_order(cuda_devi
         assert all(torch.equal(g, w) for g, w in zip(got, want[last])), (rounds, last)
 
 
+def test_disjoint_outputs_overlap_fully_and_stay_in_stream_order(cuda_device):
+    """PVA_FLAG_OUTPUTS_DISJOINT: launches into a ring of distinct output buffers do not wait for one
+    another before storing.  Results must be those of isolated launches, and whatever follows on the
+    stream (here: a device-to-host copy of the FIRST launch's output, enqueued after a chain of seven
+    launches) must see every launch complete -- a big launch followed by small ones is the case where
+    a later, shorter kernel could otherwise finish first."""
+    kw = dict(num_frames=32, slowfast_alpha=4, training=True)
+    t = pva_b200.make_transform(**kw)
+    torch.manual_seed(13)
+    big = torch.stack([synth_clip((3, 64, 256, 340), 300 + i) for i in range(8)]).cuda()
+    big_p = [t.sample_params(256, 340) for _ in range(8)]
+    small = [torch.stack([synth_clip((3, 64, 256, 340), 400 + 10 * j + i) for i in range(1)]).cuda() for j in range(3)]
+    small_p = [[t.sample_params(256, 340)] for _ in range(3)]
+    want_big = [o.clone() for o in t.run_batch(big, big_p)]
+    want_small = [[o.clone() for o in t.run_batch(c, p)] for c, p in zip(small, small_p)]
+    ring_big = [t.alloc_outputs(8, cuda_device) for _ in range(2)]
+    ring_small = [t.alloc_outputs(1, cuda_device) for _ in range(3)]
+    with pytest.raises(ValueError, match="caller-owned"):
+        t.prepare_batch(big, big_p, clips_ready=True, outputs_disjoint=True)
+    pb = [t.prepare_batch(big, big_p, out=o, clips_ready=True, outputs_disjoint=True) for o in ring_big]
+    ps = [t.prepare_batch(c, p, out=o, clips_ready=True, outputs_disjoint=True)
+          for c, p, o in zip(small, small_p, ring_small)]
+    host = [torch.empty_like(o, device="cpu").pin_memory() for o in ring_big[0]]
+    torch.cuda.synchronize()
+    for rounds in range(10):
+        for o in ring_big[rounds % 2] + [x for r in ring_small for x in r]:
+            o.zero_()
+        torch.cuda.synchronize()
+        first = pb[rounds % 2]
+        first.launch()
+        for j in range(6):
+            ps[j % 3].launch()
+        for h, o in zip(host, first.raw_out):
+            h.copy_(o, non_blocking=True)  # stream-ordered after all seven launches
+        torch.cuda.synchronize()
+        for h, w in zip(host, want_big):
+            assert torch.equal(h.permute(0, 4, 1, 2, 3), w.cpu()), rounds
+        for j in range(3):
+            assert all(torch.equal(g, w) for g, w in zip(ps[j].outputs, want_small[j])), (rounds, j)
+
+
 def test_device_results_are_not_overwritten_under_a_running_consumer(cuda_device):
     """host_out=False hands out views of the slot's device buffers.  A consumer that is still reading
     them on the current stream when the slot comes round again must be waited for: here the consumer
