@@ -316,8 +316,11 @@ class ClockSampler:
     timed region runs.  ``mark()`` brackets the region on the shared wall clock; samples inside it
     (or, for a region shorter than the period, the two samples around it) are reported."""
 
-    def __init__(self, index, period=0.002):
+    def __init__(self, index, period=0.002, enabled=True):
         self.proc = None
+        if not enabled:
+            self.t0 = self.t1 = None
+            return
         try:
             self.proc = subprocess.Popen([sys.executable, "-c", _SAMPLER_CODE, str(index), str(period)],
                                          stdin=subprocess.PIPE, stdout=subprocess.PIPE, text=True)
@@ -491,6 +494,15 @@ def run_b200_arm(args):
             dist.barrier()
         torch.cuda.synchronize(dev)
 
+    planned = {}
+
+    def plan_steps(first, count):
+        # the order of the plain launches is fixed (and the list built) before the clock starts
+        key = (first % n_sets, count)
+        if key not in planned:
+            planned[key] = [launchers[(first + j) % n_sets] for j in range(count)]
+        return planned[key]
+
     def run_steps(first, count):
         # exactly `count` steps: whole rotations come from the graph, the remainder are plain launches
         i = 0
@@ -501,15 +513,15 @@ def run_b200_arm(args):
             while count - i >= n_sets:
                 graph.replay()
                 first, i = first + n_sets, i + n_sets
-        # the order of the plain launches is fixed before the clock starts
-        todo = [launchers[(first + j) % n_sets] for j in range(count - i)]
-        for fn in todo:
+        for fn in plan_steps(first, count - i):
             fn(raw_stream)
 
-    sampler = ClockSampler(physical_gpu_index(local_rank))
+    sampler = ClockSampler(physical_gpu_index(local_rank), period=args.clock_period, enabled=not args.no_clocks)
     run_steps(0, args.warmup)
     info = _lib.last_launch_info()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    if graph is None:
+        plan_steps(args.warmup, args.steps)
     barrier()
     sampler.mark_start()
     e0.record(stream)
@@ -787,6 +799,8 @@ def main():
                     help="e2e H2D leg: whole clips, only the selected frames, or auto (see run_e2e)")
     ap.add_argument("--upload-all-frames", action="store_true",
                     help="e2e: copy whole clips to the device instead of only the frames the transform selects")
+    ap.add_argument("--no-clocks", action="store_true", help="do not sample clocks (experiments)")
+    ap.add_argument("--clock-period", dest="clock_period", type=float, default=0.002)
     ap.add_argument("--serialize-stores", action="store_true",
                     help="do not set PVA_FLAG_OUTPUTS_DISJOINT: every launch waits for the previous one before its first store")
     ap.add_argument("--planar", action="store_true",
