@@ -83,7 +83,9 @@ typedef enum PvaSrcType { PVA_SRC_U8 = 0, PVA_SRC_F32 = 1 } PvaSrcType;
  * slow_out -- e.g. consecutive batches go to different buffers of a ring, as a prefetching data
  * pipeline has them anyway.  The launch then does not wait for the previous kernel at all before it
  * stores: it fills the SMs the previous launch's slowest blocks have not reached yet, and the two
- * overlap completely.  Stream order as seen from outside is unchanged (a block of this launch does
+ * overlap completely; unless max_ctas says otherwise it also takes only half of the SMs, so that two
+ * consecutive launches run side by side, half a launch apart (better throughput for a stream of
+ * launches, a longer single launch).  Stream order as seen from outside is unchanged (a block of this launch does
  * not exit before the previous kernel has completed, so whatever follows on the stream still sees
  * both finished).  Do NOT set it when the same output buffer is handed to consecutive calls, or when
  * outputs come fresh from a caching allocator that may recycle the previous call's block. */

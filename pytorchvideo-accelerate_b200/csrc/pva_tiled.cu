@@ -1223,6 +1223,14 @@ cudaError_t launch_tiled(const KParams& p, int out_dtype, int layout, int norm, 
     const int sms = sm_count(dev);
     int grid = sms < a.g.total_tiles ? sms : a.g.total_tiles;
     if (grid > kMaxGrid) grid = kMaxGrid;
+    // Streaming regime (both flags: clips ready, outputs in a ring): a launch takes HALF the SMs and the
+    // next one starts beside it at once, so two launches are always in flight, half a launch apart.
+    // A CTA then works through twice as many tiles, which halves the share of its life spent waiting
+    // for its first tile and draining its last stores, and one launch's fill always overlaps the
+    // other's steady state.  Measured on B200, headline batch: 31.2 vs 32.6 us per launch in a long
+    // run, 33.4 vs 34.7 us over 20 launches -- at the price of a longer isolated launch (69 vs 42 us),
+    // which a caller that does not stream never pays because it does not set the flags.
+    if (a.g.pdl == 3 && p.max_ctas == 0 && grid == sms && PVA_KNOB("HALF_GRID", 1)) grid = (sms + 1) / 2;
     if (p.max_ctas > 0 && grid > p.max_ctas) grid = p.max_ctas;  // PvaPlan.max_ctas
     {
         const int cap = PVA_KNOB("MAXGRID", 0);
