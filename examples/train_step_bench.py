@@ -56,6 +56,29 @@ class SyntheticClips(torch.utils.data.Dataset):
         return self.transform({"video": self._clip, "label": i % self.num_classes})
 
 
+def micro_step(model, opt, scaler, video, label, step, accum):
+    """One micro-step of the reference's inner loop (run.py:251-261): fp16-autocast forward on
+    ``batch["video"]``, cross entropy, ``loss / accum``, scaled backward, optimiser step when
+    ``step % accum == 0`` (which fires at step 0 too, as in the reference).  Returns (loss, logits)."""
+    with torch.autocast("cuda", dtype=torch.float16):
+        logits = model(video)
+        loss = F.cross_entropy(logits, label) / accum
+    scaler.scale(loss).backward()
+    if step % accum == 0:  # run.py:258
+        scaler.step(opt)
+        scaler.update()
+        opt.zero_grad(set_to_none=True)
+    return loss.detach(), logits.detach()
+
+
+def rank_batch_sampler(n_batches, batch, rank, world):
+    """Index batches of this rank: accelerate's per-process batch sharding (run.py:196-198), stated
+    by pva_b200.batches_for_rank -- rank r takes global batches r, r + world, ..."""
+    import pva_b200
+
+    return [[b * batch + j for j in range(batch)] for b in pva_b200.batches_for_rank(n_batches, rank, world)]
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--feed", choices=["gpu", "cpu", "none"], default="gpu")
@@ -68,12 +91,14 @@ def main():
                     help="--feed gpu: the kernel reads the pinned batch in place instead of a strided upload")
     args = ap.parse_args()
 
-    rank, world, local = (int(os.environ.get(k, d)) for k, d in (("RANK", 0), ("WORLD_SIZE", 1), ("LOCAL_RANK", 0)))
+    import pva_b200
+
+    rank, world, local = pva_b200.rank_and_world()
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
         torch.distributed.init_process_group("nccl", device_id=dev)
-    torch.manual_seed(42 + rank)
+    torch.manual_seed(pva_b200.rank_seed(42, rank))
 
     model = SlowFastR50(700).to(dev).to(memory_format=torch.channels_last_3d)
     if world > 1:
@@ -83,16 +108,16 @@ def main():
 
     cores = len(os.sched_getaffinity(0))
     workers = args.workers or max(1, cores // world)
-    n_items = (args.steps + args.warmup + 4) * args.batch
-
-    import pva_b200
+    n_batches = (args.steps + args.warmup + 4) * world  # global batches; every rank takes its own share
+    n_items = n_batches * args.batch
+    batches = rank_batch_sampler(n_batches, args.batch, rank, world)
 
     kw = dict(num_frames=32, slowfast_alpha=4, training=True)  # run_slowfast_r50.sh
     t = pva_b200.make_transform(**kw, device=dev)
     to_device = None
     if args.feed == "gpu":
         ds = SyntheticClips(n_items, pva_b200.SampleParams(t))
-        loader = torch.utils.data.DataLoader(ds, batch_size=args.batch, num_workers=workers, pin_memory=True,
+        loader = torch.utils.data.DataLoader(ds, batch_sampler=batches, num_workers=workers, pin_memory=True,
                                              collate_fn=pva_b200.collate_raw_clips, persistent_workers=True,
                                              prefetch_factor=4)
         # --read-in-place: no H2D copy, the kernel reads the pinned batch over PCIe on 8 SMs
@@ -102,7 +127,7 @@ def main():
         from bench import reference_cpu_transform  # bench.py's CPU-baseline leg: the reference's transform
 
         ds = SyntheticClips(n_items, reference_cpu_transform(**kw))
-        loader = torch.utils.data.DataLoader(ds, batch_size=args.batch, num_workers=workers, pin_memory=True,
+        loader = torch.utils.data.DataLoader(ds, batch_sampler=batches, num_workers=workers, pin_memory=True,
                                              persistent_workers=True, prefetch_factor=2)
     else:
         g = torch.Generator().manual_seed(7)
@@ -112,28 +137,22 @@ def main():
         labels = torch.randint(0, 700, (args.batch,), device=dev)
         loader = [{"video": resident, "label": labels}] * (args.steps + args.warmup)
 
-    def micro_step(step, batch):
+    def step_fn(step, batch):
         if to_device is not None:
             batch = to_device(batch)
         video = [v.to(dev, non_blocking=True) for v in batch["video"]]
         label = batch["label"].to(dev, non_blocking=True)
-        with torch.autocast("cuda", dtype=torch.float16):
-            loss = F.cross_entropy(model(video), label) / args.accum
-        scaler.scale(loss).backward()
-        if step % args.accum == 0:  # run.py:258 (fires at step 0 too)
-            scaler.step(opt)
-            scaler.update()
-            opt.zero_grad(set_to_none=True)
+        micro_step(model, opt, scaler, video, label, step, args.accum)
 
     it = iter(loader)
     for s in range(args.warmup):
-        micro_step(s, next(it))
+        step_fn(s, next(it))
     torch.cuda.synchronize(dev)
     if world > 1:
         torch.distributed.barrier()
     t0 = time.perf_counter()
     for s in range(args.steps):
-        micro_step(args.warmup + s, next(it))
+        step_fn(args.warmup + s, next(it))
     torch.cuda.synchronize(dev)
     dt = time.perf_counter() - t0
     if world > 1:
