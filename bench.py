@@ -201,17 +201,35 @@ class _SyntheticClips:
         return self.transform({"video": self.clip, "label": i % 700})
 
 
+class _UntilStopped:
+    """Sampler (main process) that deals indices until told to stop, so that the loader below can be
+    run for a DURATION and still wind down by itself: once it stops, the workers finish what they
+    were handed and the iterator ends normally."""
+
+    def __init__(self):
+        self.stop = False
+
+    def __iter__(self):
+        i = 0
+        while not self.stop:
+            yield i
+            i += 1
+
+    def __len__(self):
+        return 1 << 30
+
+
 def cpu_dataloader_throughput(workload, seconds, warm_batches=2):
     """clips/s of the reference's execution model (run.py:170-176): a torch DataLoader with one
     worker per host core, batch_size = the workload's batch, default_collate, batches handed to the
     main process through shared memory."""
-    import torch
     from torch.utils.data import DataLoader
 
     wl = WORKLOADS[workload]
     workers = host_cores()
-    ds = _SyntheticClips(wl["shape"], wl["kwargs"], 1 << 20)
-    loader = DataLoader(ds, batch_size=wl["batch"], num_workers=workers, shuffle=False, pin_memory=False,
+    ds = _SyntheticClips(wl["shape"], wl["kwargs"], 1 << 30)
+    sampler = _UntilStopped()
+    loader = DataLoader(ds, batch_size=wl["batch"], sampler=sampler, num_workers=workers, pin_memory=False,
                         multiprocessing_context="spawn", persistent_workers=False)
     it = iter(loader)
     for _ in range(warm_batches + -(-workers // wl["batch"])):
@@ -223,6 +241,9 @@ def cpu_dataloader_throughput(workload, seconds, warm_batches=2):
         assert (v[0] if isinstance(v, (list, tuple)) else v).shape[0] == wl["batch"]
         n += wl["batch"]
     t1 = time.perf_counter()
+    sampler.stop = True
+    for _ in it:  # the batches already dealt out: let the workers finish them and exit cleanly
+        pass
     del it, loader
     return dict(value=n / (t1 - t0), clips=n, seconds=t1 - t0, workers=workers)
 
