@@ -24,3 +24,8 @@ done
 $CMD > $OUT/r2_plain_full.log 2>&1 && \
 ncu --set full --clock-control none --import-source on -k regex:pva_tiled -s 14 -c 2 -f -o $OUT/r2_prof_tiled $CMD > $OUT/r2_ncu_full.log 2>&1
 tail -2 $OUT/r2_ncu_full.log
+# the same traffic capture with every launch on all SMs (no PVA_FLAG_OUTPUTS_DISJOINT): what ncu, which
+# serialises launches, sees of a full-chip launch in isolation
+CMDS="python bench.py --steps 24 --warmup 8 --no-cpu-baseline --e2e-steps 5 --overlap-streams 0 --no-rehearsal --no-clocks --serialize-stores"
+$CMDS > $OUT/r2_plain_fullgrid.log 2>&1 && \
+ncu --metrics $M --cache-control none --clock-control none -k regex:pva_tiled -s 12 -c 12 --csv --log-file $OUT/r2_traffic_fullgrid_slowfast_train_b8.csv $CMDS > $OUT/r2_ncu_traffic_fullgrid.log 2>&1
