@@ -71,8 +71,7 @@ constexpr int kConsumerThreads = 512;
 constexpr int kBlockThreads = kConsumerThreads + 128;
 constexpr int kProducerRegs = 24, kConsumerRegs = 112;
 static_assert(4 * (96 - kProducerRegs) >= 16 * (kConsumerRegs - 96), "consumers would wait forever for registers");
-constexpr int kMaxStages = 5;
-constexpr int kMaxGroups = 4;
+constexpr int kMaxStages = 3;
 constexpr int kMaxStrips = 8;  // named barriers 1..8 (15 is the consumer-wide one)
 constexpr int kMaxSmem = 227 * 1024;
 constexpr int kPx = 4;  // output columns per thread
@@ -342,7 +341,7 @@ __global__ void __launch_bounds__(kBlockThreads, 1)
     // one "tile has landed" barrier per (stage, consumer group): with an odd ring depth a stage
     // alternates between the groups, and a group polling a shared barrier by parity could run two
     // phases ahead of it (bulk copies complete out of order) and take the other group's phase for its own
-    __shared__ __align__(8) unsigned long long s_full[kMaxStages * kMaxGroups];
+    __shared__ __align__(8) unsigned long long s_full[kMaxStages * 2];
     __shared__ __align__(8) unsigned long long s_empty[kMaxStages];
 
     const int tid = threadIdx.x;
@@ -355,7 +354,7 @@ __global__ void __launch_bounds__(kBlockThreads, 1)
     const int tiles_per_clip = p.n_fast * tg.bands;
 
     if (tid == 0) {
-        for (int s = 0; s < kMaxStages * kMaxGroups; ++s) {
+        for (int s = 0; s < kMaxStages * 2; ++s) {
             // bulk mode: the producer's arrive.expect_tx, the copies complete the tx count;
             // row mode: one cp.async-arrive per producer lane
             mbar_init(smem_u32(&s_full[s]), load_rows ? 32 : 1);
@@ -423,7 +422,7 @@ __global__ void __launch_bounds__(kBlockThreads, 1)
             mbar_wait(smem_u32(&s_empty[s]), ph ^ 1u);
             const int t_src = p.frame_idx[idx_row][k];
             const uint32_t st_base = in_base + (uint32_t)s * tg.stage_bytes;
-            const uint32_t bar = smem_u32(&s_full[kMaxGroups * s + grp]);
+            const uint32_t bar = smem_u32(&s_full[2 * s + grp]);
             if constexpr (kColCrop) {
                 // four tensor copies, one per row residue; a box always delivers its full size
                 // (rows or words past the tensor's extent arrive as zeros and are never read)
@@ -607,7 +606,7 @@ __global__ void __launch_bounds__(kBlockThreads, 1)
         }
 
         // every thread polls: measured faster than one poller per warp + __syncwarp (43.4 vs 46.0 us)
-        mbar_wait(smem_u32(&s_full[kMaxGroups * s + group]), ph);
+        mbar_wait(smem_u32(&s_full[2 * s + group]), ph);
         if (tid == 0 && t == t_begin) PVA_TRACE(2);  // first tile landed
 
         if (active_col && rows > 0 && !(dbg & 4)) {
@@ -952,9 +951,7 @@ bool plan_tiles(const KParams& p, int out_dtype, int layout, TileGeom* tg, const
     // candidate configurations in order of preference:
     // (consumer groups, rows per strip, input stages, staging buffers per strip)
     static const int kCand[][4] = {{2, 8, 3, 1}, {1, 4, 2, 3}, {1, 4, 3, 2}, {1, 4, 2, 2}, {1, 4, 2, 1}, {1, 2, 3, 2},
-                                   {1, 2, 2, 2}, {1, 2, 2, 1}, {1, 1, 2, 2}, {1, 1, 2, 1},
-                                   // reachable only when forced (experiments): four groups of two strips, 16-row tiles
-                                   {4, 8, 4, 1}, {4, 8, 5, 1}};
+                                   {1, 2, 2, 2}, {1, 2, 2, 1}, {1, 1, 2, 2}, {1, 1, 2, 1}};
     const int force_rps = PVA_KNOB("RPS", 0), force_bufs = PVA_KNOB("OUTBUFS", 0),
               force_stages = PVA_KNOB("STAGES", 0), force_groups = PVA_KNOB("GROUPS", 0);
     for (const auto& cand : kCand) {
@@ -963,8 +960,7 @@ bool plan_tiles(const KParams& p, int out_dtype, int layout, TileGeom* tg, const
         if (force_rps && rps != force_rps) continue;
         if (force_bufs && cand[3] != force_bufs) continue;
         if (force_stages && stages != force_stages) continue;
-        if (groups > 1 && (strips_total < groups || strips_total % groups || !bulk_ok)) continue;
-        if (groups > 1 && stages % groups != 0 && (stages % 2 == 0 && groups % 2 == 0)) continue;  // barrier period = lcm needs gcd 1 or groups | stages
+        if (groups == 2 && (strips_total < 2 || strips_total % 2 || !bulk_ok)) continue;
         const int n_strips = strips_total / groups;  // per group
         const int ytab_bytes = round_up(groups * crop * 16, 128);
         const int R = rps * n_strips;
