@@ -26,14 +26,13 @@
 // staged band keeps the source pitch and starts at the 16-byte granule of its first needed byte,
 // which makes the staged address of (row, column) LINEAR in the row index: no per-row shift.
 // The library only ever reads 16-byte granules that contain at least one byte of the clip.
-// (Two column-cropped load paths exist as experiments, both measured slower on the headline shape:
-// PVA_TILED_LOAD_ROWS=1, LDGSTS rows, and PVA_TILED_COLCROP=1, four tensor maps per clip over the rows
-// of one residue class mod 4 -- see tensor_load_4d.)
+// (Two column-cropped load paths were built and measured slower on the headline shape -- 128-bit LDGSTS
+// rows, and four tensor maps per clip over the rows of one residue class mod 4; profiles/r1_ablation.md,
+// profiles/r2_ablation.md.  They are no longer in the source.)
 //
 // Layout: T x S x S x C (channels-last, the default) or the reference's C x T x S x S.  The two differ
 // only in how a strip is staged and stored: one contiguous range of whole output rows, or three
 // ranges, one per channel plane (template parameter kPlanar).
-#include <cuda.h>  // CUtensorMap and its enums only; the encoder is looked up through the runtime
 #include <stdlib.h>
 
 #include <atomic>
@@ -75,7 +74,6 @@ constexpr int kMaxStages = 3;
 constexpr int kMaxStrips = 8;  // named barriers 1..8 (15 is the consumer-wide one)
 constexpr int kMaxSmem = 227 * 1024;
 constexpr int kPx = 4;  // output columns per thread
-constexpr int kMaxCropClips = 32;  // clips per launch of the column-cropped variant (4 tensor maps each)
 
 struct TileGeom {
     // fixed per launch, computed on the host
@@ -86,7 +84,6 @@ struct TileGeom {
     int groups;     // consumer groups (1 or 2); group g takes this CTA's tiles t_begin + g, + groups, ...
     int bands;      // ceil(crop / R)
     int rows_cap;   // source rows per plane a stage can hold
-    int pitch0;     // minimum staged row pitch; a clip uses pitch0 + ((w - pitch0) & 15) so that pitch == w (mod 16)
     int plane_stride;  // bytes between the staged planes of a tile
     int stage_bytes;
     int strip_bytes;   // staging bytes of one strip buffer
@@ -96,21 +93,14 @@ struct TileGeom {
     int pdl;         // programmatic dependent launch: 0 off, 1 wait before the first store, 2 wait at the start,
                      // 3 wait only before the CTA exits (PVA_FLAG_OUTPUTS_DISJOINT)
     int tile0_first; // the producer lets a CTA's first tile land before it requests the next ones
-    int load_rows;   // 1: column-cropped source rows through 128-bit cp.async, one row per producer lane;
-                     // 0: one cp.async.bulk per plane over the full-width row band
     int l2hint;      // bit 0: loads evict_first, bit 1: stores evict_first
     int stages;      // input ring depth (2 or 3)
     int out_bufs;    // staging buffers per strip (2 = double-buffered, 1 = wait before rewriting)
     int na_uniform;  // AFFINE: all channels share one scale, so it is folded into the row table
     int debug;       // PVA_TILED_DEBUG bits (experiments only): 1 no stores, 2 no loads, 4 no compute,
                      // 16 no proxy fence (wrong results)
-    // column-cropped loads (kColCrop): per clip, the staged row pitch in bytes (box width) and the
-    // 4-row groups a box holds; see the comment above tensor_load_4d
-    int colcrop;
     // experiments only: per-CTA time stamps (8 x uint64 %globaltimer ns per CTA) of this launch, or null
     unsigned long long* trace;
-    uint16_t cc_bw[kMaxCropClips];
-    uint16_t cc_ng[kMaxCropClips];
 };
 
 constexpr int kMaxGrid = 160;
@@ -124,11 +114,7 @@ struct TiledArgs {
     int tile_begin[kMaxGrid + 1];
 };
 
-// Column-cropped variant: the same arguments plus four tensor maps per clip (one per row residue mod 4).
-struct TiledArgsCC : TiledArgs {
-    alignas(64) CUtensorMap maps[kMaxCropClips * 4];
-};
-static_assert(sizeof(TiledArgsCC) <= 32764, "kernel parameter block limit");
+static_assert(sizeof(TiledArgs) <= 32764, "kernel parameter block limit");
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
@@ -177,24 +163,6 @@ __device__ __forceinline__ void bulk_store_hint(void* dst, uint32_t src, uint32_
     asm volatile("cp.async.bulk.global.shared::cta.bulk_group.L2::cache_hint [%0], [%1], %2, %3;" ::"l"(dst), "r"(src),
                  "r"(bytes), "l"(pol)
                  : "memory");
-}
-// Column-cropped loads.  The source row pitch (e.g. 340 B) is not a multiple of 16, which a tensor
-// map requires of its strides -- but FOUR rows are (W % 4 == 0).  So the rows of one residue class
-// (r mod 4 == k) form a legal tensor: x = 32-bit words of a row, g = r / 4 with stride 4 W, then frame
-// and channel.  Its base is the row-k address rounded down to 16 bytes (the column coordinate makes up
-// for it), its x extent ends with the row, so nothing outside the clip is ever requested.  A box must
-// START on a 16-byte boundary as well (measured: the copy faults otherwise), so the box of residue k
-// begins up to 15 bytes left of the window's first column ca, by sh_k = (address of (k, ca)) & 15.
-// One copy per residue brings the crop window's columns of `ng` row groups of all three planes:
-//   staged byte (plane c, row r, column col) = stage + (r & 3) * ksub + c * ng * bw
-//                                              + ((r >> 2) - ga) * bw + sh_(r & 3) + (col - ca)
-__device__ __forceinline__ void tensor_load_4d(uint32_t dst, const CUtensorMap* map, int x, int y, int z, int w,
-                                               uint32_t bar, uint64_t pol) {
-    asm volatile(
-        "cp.async.bulk.tensor.4d.shared::cluster.global.tile.mbarrier::complete_tx::bytes.L2::cache_hint"
-        " [%0], [%1, {%2, %3, %4, %5}], [%6], %7;" ::"r"(dst),
-        "l"(reinterpret_cast<uint64_t>(map)), "r"(x), "r"(y), "r"(z), "r"(w), "r"(bar), "l"(pol)
-        : "memory");
 }
 __device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void bulk_wait_read_all() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
@@ -305,14 +273,6 @@ __device__ __forceinline__ void stage_row_planar(unsigned char* strip, int row, 
     }
 }
 
-__device__ __forceinline__ void cp_async16(uint32_t dst, const void* src) {
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
-}
-// arrive on the mbarrier once all cp.async issued so far by this thread have landed
-__device__ __forceinline__ void cp_async_arrive(uint32_t bar) {
-    asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(bar) : "memory");
-}
-
 // Two bytes of t (compile-time positions) as a half2 of fp16 SUBNORMALS: the 16-bit pattern
 // 0x00bb is exactly b * 2^-24, so zero-extension is the whole integer->float conversion and
 // cvt.f32.f16 finishes it.  The 2^24 is folded into the row weights.
@@ -325,10 +285,8 @@ __device__ __forceinline__ __half2 bytes_as_half2(uint32_t t) {
 // kNormT: 0 = EXACT, 1 = AFFINE with one scale for all channels (folded into the row table),
 // 2 = AFFINE with per-channel scales.  kPlanar: write C x T x S x S (the reference's order) instead of
 // T x S x S x C.
-template <typename OutT, int kNormT, bool kFastX, bool kPlanar, bool kColCrop>
-__global__ void __launch_bounds__(kBlockThreads, 1)
-    pva_tiled_kernel(const __grid_constant__ typename std::conditional<kColCrop, TiledArgsCC, TiledArgs>::type a) {
-    static_assert(!kColCrop || kFastX, "column-cropped loads come with the aligned-window x-pass");
+template <typename OutT, int kNormT, bool kFastX, bool kPlanar>
+__global__ void __launch_bounds__(kBlockThreads, 1) pva_tiled_kernel(const __grid_constant__ TiledArgs a) {
     extern __shared__ __align__(128) unsigned char smem[];
     constexpr int kNorm = kNormT == 0 ? kNormExact : kNormAffine;
     constexpr bool kUniformNa = kNormT == 1;
@@ -336,7 +294,6 @@ __global__ void __launch_bounds__(kBlockThreads, 1)
     const TileGeom& tg = a.g;
     // measurement-only switches (see kExperiments): compile-time constants in the production library
     const int dbg = kExperiments ? tg.debug : 0;
-    const bool load_rows = kExperiments && tg.load_rows;
     const int l2hint = kExperiments ? tg.l2hint : 3;
     // one "tile has landed" barrier per (stage, consumer group): with an odd ring depth a stage
     // alternates between the groups, and a group polling a shared barrier by parity could run two
@@ -355,9 +312,8 @@ __global__ void __launch_bounds__(kBlockThreads, 1)
 
     if (tid == 0) {
         for (int s = 0; s < kMaxStages * 2; ++s) {
-            // bulk mode: the producer's arrive.expect_tx, the copies complete the tx count;
-            // row mode: one cp.async-arrive per producer lane
-            mbar_init(smem_u32(&s_full[s]), load_rows ? 32 : 1);
+            // the producer's arrive.expect_tx; the copies complete the tx count
+            mbar_init(smem_u32(&s_full[s]), 1);
             if (s < kMaxStages) mbar_init(smem_u32(&s_empty[s]), kConsumerThreads / 32 / tg.groups);  // the warps of the group that consumed the tile
         }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -392,10 +348,9 @@ __global__ void __launch_bounds__(kBlockThreads, 1)
         if (tid >= kConsumerThreads + 32) return;  // the other three warps only existed to give registers away
         const int lane = tid - kConsumerThreads;
         const uint64_t pol = l2_evict_first_policy();
-        int cur_clip = -1, ca = 0, ncols = 0, W = 0, H = 0, T_in = 0, pitch = 0, top = 0, idx_row = 0;
+        int cur_clip = -1, ca = 0, ncols = 0, W = 0, H = 0, T_in = 0, top = 0, idx_row = 0;
         float sy = 0.f;
         const uint8_t* src = nullptr;
-        uint32_t cc_bw = 0, cc_ng = 0, cc_ksub = 0;  // kColCrop: box width (bytes), row groups per box, bytes per residue
         int s = 0;
         uint32_t ph = 0;
         for (int t = t_begin; t < t_end; ++t) {
@@ -409,11 +364,6 @@ __global__ void __launch_bounds__(kBlockThreads, 1)
                 const ClipGeom& g = p.clips[clip_i];
                 src = g.src, W = g.w, H = g.h, T_in = g.t_in, sy = g.sy, top = g.top, idx_row = g.idx_row;
                 src_range(g.sx, g.left, g.left + crop - 1, g.w, ca, ncols);
-                pitch = load_rows ? tg.pitch0 + ((W - tg.pitch0) & 15) : W;
-                if constexpr (kColCrop) {
-                    cc_bw = tg.cc_bw[clip_i], cc_ng = tg.cc_ng[clip_i];
-                    cc_ksub = (3u * cc_ng * cc_bw + 127u) & ~127u;
-                }
             }
             const int yb = band * tg.R;
             const int ye = min(yb + tg.R, crop);
@@ -423,37 +373,7 @@ __global__ void __launch_bounds__(kBlockThreads, 1)
             const int t_src = p.frame_idx[idx_row][k];
             const uint32_t st_base = in_base + (uint32_t)s * tg.stage_bytes;
             const uint32_t bar = smem_u32(&s_full[2 * s + grp]);
-            if constexpr (kColCrop) {
-                // four tensor copies, one per row residue; a box always delivers its full size
-                // (rows or words past the tensor's extent arrive as zeros and are never read)
-                if (lane == 0) mbar_arrive_expect_tx(bar, (dbg & 2) ? 0u : 12u * cc_ng * cc_bw);
-                __syncwarp();
-                if (lane < 4 && !(dbg & 2)) {
-                    const uint32_t delta = (uint32_t)(((uintptr_t)src + (size_t)lane * W) & 15);
-                    tensor_load_4d(st_base + (uint32_t)lane * cc_ksub, &a.maps[clip_i * 4 + lane],
-                                   (int)((((uint32_t)ca + delta) & ~15u) >> 2), ra >> 2, t_src, 0, bar, pol);
-                }
-            } else if (load_rows) {
-                // Column-cropped rows, one source row per lane and pass: each lane walks its row in
-                // 16-byte granules (global and shared side both aligned because pitch == W mod 16).
-                // Staged byte (rr, col) sits at plane base + (gc & 15) + rr * pitch + (col - ca).
-                if (!(dbg & 2)) {
-                    const int n_rows_all = 3 * nrows;
-                    for (int j = lane; j < n_rows_all; j += 32) {
-                        const int c = j / nrows, rr = j - c * nrows;
-                        const uint8_t* gc = src + (((size_t)c * T_in + t_src) * H + ra) * W + ca;
-                        const uint8_t* ga = gc + (size_t)rr * W;
-                        const uint32_t sh = (uint32_t)((uintptr_t)ga & 15);
-                        const int n16 = (int)((sh + ncols + 15) >> 4);  // granules holding a needed byte
-                        const uint8_t* al = ga - sh;
-                        uint32_t dst = st_base + (uint32_t)c * tg.plane_stride + (uint32_t)((uintptr_t)gc & 15) +
-                                       (uint32_t)rr * pitch - sh;
-#pragma unroll 4
-                        for (int q = 0; q < n16; ++q) cp_async16(dst + 16 * q, al + 16 * q);
-                    }
-                }
-                cp_async_arrive(bar);
-            } else {
+            {
                 // One bulk copy per plane: the whole band of source rows, first needed byte (ra, ca)
                 // to last needed byte, rounded out to 16-byte granules.  Rows are contiguous in
                 // memory, so this is a single linear range; staged byte (r, col) sits at
@@ -479,7 +399,6 @@ __global__ void __launch_bounds__(kBlockThreads, 1)
             if (tg.tile0_first && t == t_begin) mbar_wait(bar, 0u);
             if (++s == n_stages) s = 0, ph ^= 1u;
         }
-        if (load_rows) asm volatile("cp.async.wait_all;" ::: "memory");  // no copy may outlive the CTA
         if (lane == 0) PVA_TRACE(7);  // all loads issued
         return;
     }
@@ -507,7 +426,7 @@ __global__ void __launch_bounds__(kBlockThreads, 1)
 
     // per-clip state, cached in registers
     int cur_clip = -1;
-    int ca = 0, W = 0, H = 0, T_in = 0, pitch = 0, idx_row = 0;
+    int ca = 0, W = 0, H = 0, T_in = 0, idx_row = 0;
     const uint8_t* src = nullptr;
     int woff = 0;               // kFastX: byte offset (from column ca) of the thread's aligned 8-byte window
     uint32_t sel0 = 0, sel1 = 0;  // kFastX: PRMT selectors picking the 4 left / right taps out of the window
@@ -539,33 +458,15 @@ __global__ void __launch_bounds__(kBlockThreads, 1)
             cur_clip = clip_i;
             const ClipGeom& g = p.clips[clip_i];
             src = g.src, W = g.w, H = g.h, T_in = g.t_in, idx_row = g.idx_row;
-            // staged pitch: the source pitch itself (band copies) or the cropped pitch congruent to it mod 16
-            pitch = load_rows ? tg.pitch0 + ((W - tg.pitch0) & 15) : W;
             // AFFINE: the row weights absorb the 2^24 of the subnormal trick and, when all
             // channels share it, the normalisation scale 1 / (255 std)
             const float wscale = (kNorm == kNormAffine) ? 16777216.0f * (kUniformNa ? p.na[0] : 1.0f) : 1.0f;
-            uint32_t cc_bw = 0, cc_ksub = 0, cc_ca = 0;
-            if constexpr (kColCrop) {
-                cc_bw = tg.cc_bw[clip_i];
-                cc_ksub = (3u * tg.cc_ng[clip_i] * cc_bw + 127u) & ~127u;
-                int c0, n0;
-                src_range(g.sx, g.left, g.left + crop - 1, g.w, c0, n0);
-                cc_ca = (uint32_t)c0;
-            }
             for (int i = g_col; i < tg.bands * tg.rps && in_strip; i += strip_threads) {
                 const int y = (i / tg.rps) * tg.R + strip * tg.rps + (i % tg.rps);
                 if (y >= crop) continue;
                 int y0, y1;
                 float l0, l1;
                 bilinear_taps(g.sy, g.top + y, g.h, y0, y1, l0, l1);
-                if constexpr (kColCrop) {
-                    // the table holds staged row OFFSETS (residue block + group row + the residue's
-                    // alignment shift), not row numbers; within a tile they identify a row just as well
-                    const uint32_t sh0 = (uint32_t)((uintptr_t)g.src + (size_t)(y0 & 3) * g.w + cc_ca) & 15u;
-                    const uint32_t sh1 = (uint32_t)((uintptr_t)g.src + (size_t)(y1 & 3) * g.w + cc_ca) & 15u;
-                    y0 = (int)((uint32_t)(y0 & 3) * cc_ksub + (uint32_t)(y0 >> 2) * cc_bw + sh0);
-                    y1 = (int)((uint32_t)(y1 & 3) * cc_ksub + (uint32_t)(y1 >> 2) * cc_bw + sh1);
-                }
                 ytab[y] = make_int4(y0, y1, __float_as_int(l0 * wscale), __float_as_int(l1 * wscale));
             }
             int dummy;
@@ -610,20 +511,9 @@ __global__ void __launch_bounds__(kBlockThreads, 1)
         if (tid == 0 && t == t_begin) PVA_TRACE(2);  // first tile landed
 
         if (active_col && rows > 0 && !(dbg & 4)) {
-            // staged address of (plane c, source row r, window start) = rowbase[c] + r * pitch
-            // (kColCrop: rowbase[c] + the row's offset from the table)
+            // staged address of (plane c, source row r, window start) = rowbase[c] + r * W
             uint32_t rowbase[3];
-            if constexpr (kColCrop) {
-                const ClipGeom& g = p.clips[clip_i];
-                int ra, rb;
-                float l0, l1;
-                bilinear_taps(g.sy, g.top + yb, g.h, ra, rb, l0, l1);  // first source row of the tile
-                const uint32_t bw = tg.cc_bw[clip_i], ng = tg.cc_ng[clip_i];
-#pragma unroll
-                for (int c = 0; c < 3; ++c)
-                    rowbase[c] = in_base + (uint32_t)s * tg.stage_bytes + (uint32_t)c * ng * bw -
-                                 (uint32_t)(ra >> 2) * bw + (uint32_t)woff;
-            } else {
+            {
                 int ra;  // first source row staged for this tile (row yb of the table belongs to strip 0)
                 {
                     const ClipGeom& g = p.clips[clip_i];
@@ -636,7 +526,7 @@ __global__ void __launch_bounds__(kBlockThreads, 1)
                 for (int c = 0; c < 3; ++c) {
                     const uint32_t gc = (uint32_t)(uintptr_t)(src + (((size_t)c * T_in + t_src) * H + ra) * W + ca);
                     rowbase[c] = in_base + (uint32_t)s * tg.stage_bytes + (uint32_t)c * tg.plane_stride + (gc & 15u) +
-                                 (uint32_t)(kFastX ? woff : 0) - (uint32_t)ra * (uint32_t)pitch;
+                                 (uint32_t)(kFastX ? woff : 0) - (uint32_t)ra * (uint32_t)W;
                 }
             }
 
@@ -644,7 +534,7 @@ __global__ void __launch_bounds__(kBlockThreads, 1)
             //   EXACT : h = fma(lx0, lut[b0], lx1 * lut[b1])            (ATen's arithmetic)
             //   AFFINE: h = fma(lx1, b1 - b0, b0) * 2^-24               (same value, one rounding)
             auto hrow = [&](int r, float (&h)[kPx][3]) {
-                const uint32_t ro = kColCrop ? (uint32_t)r : (uint32_t)r * (uint32_t)pitch;
+                const uint32_t ro = (uint32_t)r * (uint32_t)W;
 #pragma unroll
                 for (int c = 0; c < 3; ++c) {
                     const uint32_t addr = rowbase[c] + ro;
@@ -860,51 +750,8 @@ void host_taps(float scale, int dst, int in_size, int* i0, int* i1) {
     *i1 = b;
 }
 
-#ifdef PVA_EXPERIMENTS
-typedef CUresult (*TensorMapEncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
-                                      const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
-                                      CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-
-// cuTensorMapEncodeTiled through the runtime (the library does not link libcuda); nullptr if the
-// driver does not offer it -- the linear band copies are used then.
-TensorMapEncodeFn tensor_map_encoder() {
-    static TensorMapEncodeFn fn = [] {
-        void* sym = nullptr;
-        cudaDriverEntryPointQueryResult q = cudaDriverEntryPointSymbolNotFound;
-        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &sym, cudaEnableDefault, &q) != cudaSuccess ||
-            q != cudaDriverEntryPointSuccess) {
-            (void)cudaGetLastError();
-            sym = nullptr;
-        }
-        return reinterpret_cast<TensorMapEncodeFn>(sym);
-    }();
-    return fn;
-}
-
-// Column-cropped loads need, for every clip of the launch: rows of whole 32-bit words whose groups of
-// four keep 16-byte alignment from plane to plane, up-scaling or identity in x (the aligned-window
-// x-pass), and a parameter block that can hold the maps.
-//
-// Experiments build only, and there OFF unless PVA_TILED_COLCROP=1.  Measured on B200 (profiles/r1_ablation.md): it cuts the DRAM read
-// bytes by about 20 %, but the TMA unit walks a box row by row (272-byte rows here, ~25 cycles each),
-// so the loads alone take 20.0 us per headline launch against 15.7 us for the linear band copies.
-// Net: 37.4 vs 35.7 us at batch 8, 130.3 vs 132.9 us at batch 32.  Kept, parity-tested, for shapes
-// where the window is a small part of a wide frame.
-bool colcrop_eligible(const KParams& p) {
-    if (!PVA_KNOB("COLCROP", 0) || PVA_KNOB("LOAD_ROWS", 0)) return false;
-    if (p.n_clips > kMaxCropClips) return false;
-    for (int i = 0; i < p.n_clips; ++i) {
-        const ClipGeom& g = p.clips[i];
-        if (g.w % 4 || g.h < 4 || ((size_t)g.h * g.w) % 16 || (uintptr_t)g.src % 4 || g.w > g.ow) return false;
-    }
-    return tensor_map_encoder() != nullptr;
-}
-#else
-bool colcrop_eligible(const KParams&) { return false; }
-#endif
-
 // Choose rows-per-strip, ring depth and the shared-memory carve-up; false if nothing fits.
-bool plan_tiles(const KParams& p, int out_dtype, int layout, TileGeom* tg, const char** why, bool want_colcrop = false) {
+bool plan_tiles(const KParams& p, int out_dtype, int layout, TileGeom* tg, const char** why) {
     if (layout != kLayoutTHWC && layout != kLayoutCTHW) {
         *why = "unknown output layout";
         return false;
@@ -929,19 +776,6 @@ bool plan_tiles(const KParams& p, int out_dtype, int layout, TileGeom* tg, const
     const int esz = out_dtype == 0 ? 4 : 2;
     const int row_bytes = crop * 3 * esz;
 
-    int max_cols = 0;
-    for (int i = 0; i < p.n_clips; ++i) {
-        const ClipGeom& g = p.clips[i];
-        int a0, a1, b0, b1;
-        host_taps(g.sx, g.left, g.w, &a0, &a1);
-        host_taps(g.sx, g.left + crop - 1, g.w, &b0, &b1);
-        max_cols = max_cols > (b1 - a0 + 1) ? max_cols : (b1 - a0 + 1);
-    }
-    const int load_rows = PVA_KNOB("LOAD_ROWS", 0);
-    bool colcrop = want_colcrop;
-    // row mode: rows of a staged plane must not overlap; a copy spills up to 15 bytes on either side
-    const int pitch0 = max_cols + 15;
-    const int pitch_max = pitch0 + 15;
     const int lut_bytes = 3 * 256 * 4;
     // a bulk store covers whole output rows (T x S x S x C) or whole rows of one channel plane (C x T x S x S)
     const int store_unit = layout == kLayoutCTHW ? crop * esz : row_bytes;
@@ -984,43 +818,8 @@ bool plan_tiles(const KParams& p, int out_dtype, int layout, TileGeom* tg, const
             }
         }
         // + 15 leading alignment bytes, rounded to a granule, + the 8-byte tap window overhang
-        const int plane_stride = load_rows ? round_up(rows_cap * pitch_max + 48, 16) : round_up(band_bytes + 15 + 16 + 8, 16);
-        int stage_bytes = round_up(3 * plane_stride, 128);
-        if (colcrop) {
-            // per clip: box width = the window's columns from the word that holds the first one, in
-            // whole 16-byte units; row groups per box = the most any band of this clip spans
-            int ksub_max = 0;
-            for (int i = 0; i < p.n_clips; ++i) {
-                const ClipGeom& g = p.clips[i];
-                int c0, c1, d0, d1;
-                host_taps(g.sx, g.left, g.w, &c0, &c1);
-                host_taps(g.sx, g.left + crop - 1, g.w, &d0, &d1);
-                int sh_max = 0;  // a box starts on the 16-byte boundary at or before the window's first column
-                for (int k = 0; k < 4; ++k) {
-                    const int sh = (int)(((uintptr_t)g.src + (size_t)k * g.w + c0) & 15);
-                    sh_max = sh_max > sh ? sh_max : sh;
-                }
-                const int bw = round_up(sh_max + (d1 - c0 + 1), 16);
-                int ng = 1;
-                for (int b = 0; b < bands; ++b) {
-                    const int yb = b * R, ye = (yb + R < crop ? yb + R : crop);
-                    int a0, a1, b0, b1;
-                    host_taps(g.sy, g.top + yb, g.h, &a0, &a1);
-                    host_taps(g.sy, g.top + ye - 1, g.h, &b0, &b1);
-                    const int n = (b1 >> 2) - (a0 >> 2) + 1;
-                    ng = ng > n ? ng : n;
-                }
-                if (bw / 4 > 256 || ng > 256) {
-                    colcrop = false;  // a box side holds at most 256 elements
-                    break;
-                }
-                tg->cc_bw[i] = (uint16_t)bw;
-                tg->cc_ng[i] = (uint16_t)ng;
-                const int ksub = round_up(3 * ng * bw, 128);
-                ksub_max = ksub_max > ksub ? ksub_max : ksub;
-            }
-            if (colcrop) stage_bytes = 4 * ksub_max + 128;  // + the tap window's overhang past the last row
-        }
+        const int plane_stride = round_up(band_bytes + 15 + 16 + 8, 16);
+        const int stage_bytes = round_up(3 * plane_stride, 128);
         const int strip_bytes = round_up(rps * row_bytes, 128);
         int off = 0;
         tg->off_ytab = off;
@@ -1040,8 +839,6 @@ bool plan_tiles(const KParams& p, int out_dtype, int layout, TileGeom* tg, const
         tg->n_strips = n_strips;
         tg->bands = bands;
         tg->rows_cap = rows_cap;
-        tg->pitch0 = pitch0;
-        tg->load_rows = load_rows;
         tg->plane_stride = plane_stride;
         tg->stage_bytes = stage_bytes;
         tg->strip_bytes = strip_bytes;
@@ -1053,19 +850,12 @@ bool plan_tiles(const KParams& p, int out_dtype, int layout, TileGeom* tg, const
         tg->total_tiles = p.n_clips * p.n_fast * bands;
         tg->na_uniform = (p.na[0] == p.na[1] && p.na[1] == p.na[2]) ? 1 : 0;
         tg->debug = PVA_KNOB("DEBUG", 0);
-        tg->colcrop = colcrop ? 1 : 0;
         tg->trace = nullptr;
         return true;
     }
     *why = "tile does not fit shared memory (source rows too wide for this scale)";
     return false;
 }
-
-#ifdef PVA_EXPERIMENTS
-using LaunchArgs = TiledArgsCC;
-#else
-using LaunchArgs = TiledArgs;  // the column-cropped variant is not part of the production library
-#endif
 
 // Per-device facts, looked up once per process (relaxed atomics: racing threads store the same value).
 constexpr int kMaxDevices = 64;
@@ -1084,9 +874,9 @@ int sm_count(int dev) {
     return sms;
 }
 
-template <typename OutT, int N, bool F, bool kPlanar, bool kColCrop, typename Args>
-cudaError_t launch_one(const Args& a, int dev, int grid, int smem, cudaStream_t stream) {
-    auto kern = pva_tiled_kernel<OutT, N, F, kPlanar, kColCrop>;
+template <typename OutT, int N, bool F, bool kPlanar>
+cudaError_t launch_one(const TiledArgs& a, int dev, int grid, int smem, cudaStream_t stream) {
+    auto kern = pva_tiled_kernel<OutT, N, F, kPlanar>;
     // The opt-in shared-memory ceiling only ever needs raising (per device, per variant).  This is
     // the one piece of process-wide state the library keeps: a high-water mark per device, updated
     // with relaxed atomics (two threads racing here both make the same idempotent call).
@@ -1115,18 +905,9 @@ cudaError_t launch_one(const Args& a, int dev, int grid, int smem, cudaStream_t 
 }
 
 template <typename OutT, bool kPlanar>
-cudaError_t launch_t(const LaunchArgs& a, int norm, bool fastx, int dev, int grid, int smem, cudaStream_t stream) {
-#ifdef PVA_EXPERIMENTS
-    if (a.g.colcrop) {  // implies fastx
-        if (norm == 0) return launch_one<OutT, 0, true, kPlanar, true, TiledArgsCC>(a, dev, grid, smem, stream);
-        if (norm == 1) return launch_one<OutT, 1, true, kPlanar, true, TiledArgsCC>(a, dev, grid, smem, stream);
-        if (norm == 2) return launch_one<OutT, 2, true, kPlanar, true, TiledArgsCC>(a, dev, grid, smem, stream);
-        return cudaErrorInvalidValue;
-    }
-#endif
-    const TiledArgs& b = a;
+cudaError_t launch_t(const TiledArgs& a, int norm, bool fastx, int dev, int grid, int smem, cudaStream_t stream) {
 #define PVA_TILED_CASE(N, F) \
-    if (norm == N && fastx == F) return launch_one<OutT, N, F, kPlanar, false, TiledArgs>(b, dev, grid, smem, stream);
+    if (norm == N && fastx == F) return launch_one<OutT, N, F, kPlanar>(a, dev, grid, smem, stream);
     PVA_TILED_CASE(0, false)
     PVA_TILED_CASE(0, true)
     PVA_TILED_CASE(1, false)
@@ -1137,55 +918,20 @@ cudaError_t launch_t(const LaunchArgs& a, int norm, bool fastx, int dev, int gri
     return cudaErrorInvalidValue;
 }
 
-#ifdef PVA_EXPERIMENTS
-// The four residue-class tensors of one clip (see tensor_load_4d).
-bool encode_clip_maps(const ClipGeom& g, int bw, int ng, CUtensorMap* maps) {
-    TensorMapEncodeFn enc = tensor_map_encoder();
-    if (!enc) return false;
-    for (int k = 0; k < 4; ++k) {
-        const uintptr_t row_k = (uintptr_t)g.src + (size_t)k * g.w;
-        const uintptr_t delta = row_k & 15;
-        const cuuint64_t dims[4] = {(cuuint64_t)((delta + g.w) / 4), (cuuint64_t)((g.h - k + 3) / 4), (cuuint64_t)g.t_in, 3};
-        const cuuint64_t strides[3] = {(cuuint64_t)4 * g.w, (cuuint64_t)g.h * g.w, (cuuint64_t)g.t_in * g.h * g.w};
-        const cuuint32_t box[4] = {(cuuint32_t)(bw / 4), (cuuint32_t)ng, 1, 3};
-        const cuuint32_t estr[4] = {1, 1, 1, 1};
-        if (enc(&maps[k], CU_TENSOR_MAP_DATA_TYPE_UINT32, 4, reinterpret_cast<void*>(row_k - delta), dims, strides, box,
-                estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
-                (CUtensorMapL2promotion)PVA_KNOB("CC_PROMO", 0),
-                CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
-            return false;
-    }
-    return true;
-}
-#endif
-
 }  // namespace
 
 cudaError_t launch_tiled(const KParams& p, int out_dtype, int layout, int norm, cudaStream_t stream, TiledConfig* cfg,
                          const char** why) {
-    // The argument block (~14 KB; ~30 KB with the experiments' tensor maps) lives on this call's
-    // stack: nothing survives the call.
-    LaunchArgs a;
+    // The argument block (~14 KB) lives on this call's stack: nothing survives the call.
+    TiledArgs a;
     *why = nullptr;
     const char* reason = "";
     // one plan per launch: it both decides whether the tiled kernel can take the shapes and carves
     // up shared memory
-    if (!plan_tiles(p, out_dtype, layout, &a.g, &reason, colcrop_eligible(p))) {
+    if (!plan_tiles(p, out_dtype, layout, &a.g, &reason)) {
         *why = reason;
         return cudaErrorNotSupported;
     }
-#ifdef PVA_EXPERIMENTS
-    if (a.g.colcrop) {
-        bool encoded = true;
-        for (int i = 0; i < p.n_clips && encoded; ++i)
-            encoded = encode_clip_maps(p.clips[i], a.g.cc_bw[i], a.g.cc_ng[i], &a.maps[4 * i]);
-        // the driver refused a map: plan again for the linear band copies
-        if (!encoded && !plan_tiles(p, out_dtype, layout, &a.g, &reason, false)) {
-            *why = reason;
-            return cudaErrorNotSupported;
-        }
-    }
-#endif
     // the fast x-path needs, for every clip of the launch: up-scaling or identity in x (so that
     // the taps of 4 adjacent outputs fit an aligned 8-byte window) and 4-byte aligned rows
     bool fastx = true;
@@ -1193,7 +939,7 @@ cudaError_t launch_tiled(const KParams& p, int out_dtype, int layout, int norm, 
         const ClipGeom& g = p.clips[i];
         fastx = fastx && (g.w <= g.ow) && (g.w % 4 == 0) && ((uintptr_t)g.src % 4 == 0);
     }
-    static_cast<TiledArgs&>(a).p = p;
+    a.p = p;
     // 2: wait for the previous kernel before touching memory at all; 1 (PVA_FLAG_CLIPS_READY): only
     // before the first store; 3 (+ PVA_FLAG_OUTPUTS_DISJOINT): only before the CTA exits.  Only the
     // caller's explicit flags ever relax the ordering.
