@@ -419,6 +419,11 @@ __global__ void __launch_bounds__(kBlockThreads, 1) pva_tiled_kernel(const __gri
     const bool active_col = g_col < gx && in_strip;
     const bool full_group = (kPx * g_col + kPx) <= crop && (crop & 3) == 0;  // vector staging stores need crop % 4 == 0
     const int strip_threads = tg.tps;
+    // Threads that hand a strip to the store engine: thread 0 of the strip; in the C x T x S x S order the
+    // strip's first three threads, one channel plane each, so that the three copies are issued side by
+    // side instead of one after the other (36.6 -> 35.5 us per headline launch; six threads, with the slow
+    // pathway's copies on their own, measured the same).
+    const bool issuer = kPlanar ? g_col < 3 : g_col == 0;
     int4* ytab = reinterpret_cast<int4*>(smem + tg.off_ytab) + (size_t)group * crop;  // one row table per group
     unsigned char* out_base = smem + tg.off_out + (size_t)(group * tg.n_strips + strip) * tg.out_bufs * tg.strip_bytes;
     const float* lut = reinterpret_cast<const float*>(smem + tg.off_lut);
@@ -502,7 +507,7 @@ __global__ void __launch_bounds__(kBlockThreads, 1) pva_tiled_kernel(const __gri
 
         if (tg.out_bufs == 1 && tg.bulk_store && in_strip) {
             // single staging buffer: the previous tile's store must have drained it
-            if (g_col == 0) bulk_wait_read_all();
+            if (issuer) bulk_wait_read_all();
             named_bar(bar_strip, strip_threads);
         }
 
@@ -650,12 +655,12 @@ __global__ void __launch_bounds__(kBlockThreads, 1) pva_tiled_kernel(const __gri
                 if (!(dbg & 16)) fence_async_smem();  // generic-proxy writes of the strip -> visible to the async proxy
                 // double-buffered: the other buffer's store (issued a tile ago) must have drained
                 // before anyone runs ahead into the next tile and overwrites it
-                if (g_col == 0) {
+                if (issuer) {
                     if (tg.out_bufs == 2) bulk_wait_read_all();
                     if (tg.out_bufs == 3) bulk_wait_read_but_one();  // the store before last has drained
                 }
                 named_bar(bar_strip, strip_threads);
-                if (g_col == 0 && rows > 0 && !(dbg & 1)) {
+                if (issuer && rows > 0 && !(dbg & 1)) {
                     if (tid == 0 && t == t_begin) PVA_TRACE(3);  // first strip computed, about to store
                     if (!may_store) {
                         asm volatile("griddepcontrol.wait;" ::: "memory");
@@ -668,21 +673,19 @@ __global__ void __launch_bounds__(kBlockThreads, 1) pva_tiled_kernel(const __gri
                         const uint32_t bytes = (uint32_t)((size_t)rows * crop * esz);
                         const uint32_t sstep = (uint32_t)((size_t)tg.rps * crop * esz);
                         const uint64_t pol = l2_evict_first_policy();
-#pragma unroll
-                        for (int c = 0; c < 3; ++c) {
+                        const int c = g_col;  // this thread's plane
+                        {
                             OutT* d = fast + (((size_t)c * p.n_fast + k) * crop + y_begin) * crop;
                             if (l2hint & 2) bulk_store_hint(d, ssrc + c * sstep, bytes, pol);
                             else bulk_store(d, ssrc + c * sstep, bytes);
                         }
                         if (slow)
                             for (int j = 0; j < p.n_slow; ++j)
-                                if (p.slow_idx[j] == k)
-#pragma unroll
-                                    for (int c = 0; c < 3; ++c) {
-                                        OutT* d = slow + (((size_t)c * p.n_slow + j) * crop + y_begin) * crop;
-                                        if (l2hint & 2) bulk_store_hint(d, ssrc + c * sstep, bytes, pol);
-                                        else bulk_store(d, ssrc + c * sstep, bytes);
-                                    }
+                                if (p.slow_idx[j] == k) {
+                                    OutT* d = slow + (((size_t)c * p.n_slow + j) * crop + y_begin) * crop;
+                                    if (l2hint & 2) bulk_store_hint(d, ssrc + c * sstep, bytes, pol);
+                                    else bulk_store(d, ssrc + c * sstep, bytes);
+                                }
                     } else {
                     const uint32_t bytes = (uint32_t)((size_t)rows * crop * 3 * esz);
                     if (l2hint & 2) {
@@ -733,7 +736,7 @@ __global__ void __launch_bounds__(kBlockThreads, 1) pva_tiled_kernel(const __gri
     // the staging buffers must outlive the stores' reads; the writes themselves complete with the kernel
     if (tid == 0) PVA_TRACE(5);  // last tile of group 0 handed to the store engine
     if (tg.pdl == 3 && tid == 0) asm volatile("griddepcontrol.wait;" ::: "memory");  // completion stays transitive
-    if (tg.bulk_store && g_col == 0 && in_strip) bulk_wait_read_all();
+    if (tg.bulk_store && issuer && in_strip) bulk_wait_read_all();
     if (tid == 0) PVA_TRACE(6);  // staging drained: CTA about to exit
 }
 
