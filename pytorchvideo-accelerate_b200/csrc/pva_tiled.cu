@@ -423,7 +423,7 @@ __global__ void __launch_bounds__(kBlockThreads, 1) pva_tiled_kernel(const __gri
     // strip's first three threads, one channel plane each, so that the three copies are issued side by
     // side instead of one after the other (36.6 -> 35.5 us per headline launch; six threads, with the slow
     // pathway's copies on their own, measured the same).
-    const bool issuer = kPlanar ? g_col < 3 : g_col == 0;
+    const bool issuer = kPlanar ? g_col < 3 : (g_col == 0 || (g_col == 32 && p.slow_out != nullptr && tg.tps > 32));
     int4* ytab = reinterpret_cast<int4*>(smem + tg.off_ytab) + (size_t)group * crop;  // one row table per group
     unsigned char* out_base = smem + tg.off_out + (size_t)(group * tg.n_strips + strip) * tg.out_bufs * tg.strip_bytes;
     const float* lut = reinterpret_cast<const float*>(smem + tg.off_lut);
@@ -688,16 +688,19 @@ __global__ void __launch_bounds__(kBlockThreads, 1) pva_tiled_kernel(const __gri
                                 }
                     } else {
                     const uint32_t bytes = (uint32_t)((size_t)rows * crop * 3 * esz);
+                    // thread 0 of the strip sends the fast pathway's copy, the first thread of the strip's second
+                    // warp the slow pathway's (a strip of one warp: thread 0 sends both)
+                    const bool do_fast = g_col == 0, do_slow = slow && (g_col == 32 || tg.tps <= 32);
                     if (l2hint & 2) {
                         const uint64_t pol = l2_evict_first_policy();
-                        bulk_store_hint(fast + ((size_t)k * crop + y_begin) * crop * 3, ssrc, bytes, pol);
-                        if (slow)
+                        if (do_fast) bulk_store_hint(fast + ((size_t)k * crop + y_begin) * crop * 3, ssrc, bytes, pol);
+                        if (do_slow)
                             for (int j = 0; j < p.n_slow; ++j)
                                 if (p.slow_idx[j] == k)
                                     bulk_store_hint(slow + ((size_t)j * crop + y_begin) * crop * 3, ssrc, bytes, pol);
                     } else {
-                        bulk_store(fast + ((size_t)k * crop + y_begin) * crop * 3, ssrc, bytes);
-                        if (slow)
+                        if (do_fast) bulk_store(fast + ((size_t)k * crop + y_begin) * crop * 3, ssrc, bytes);
+                        if (do_slow)
                             for (int j = 0; j < p.n_slow; ++j)
                                 if (p.slow_idx[j] == k) bulk_store(slow + ((size_t)j * crop + y_begin) * crop * 3, ssrc, bytes);
                     }
