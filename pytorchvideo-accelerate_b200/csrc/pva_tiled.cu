@@ -182,6 +182,7 @@ __device__ __forceinline__ uint32_t lds8(uint32_t addr) {
     return v;
 }
 
+constexpr int kTraceWords = 128;  // uint64 words per CTA and launch in the experiments' trace buffer
 __device__ __forceinline__ unsigned long long global_ns() {
     unsigned long long t;
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
@@ -190,7 +191,14 @@ __device__ __forceinline__ unsigned long long global_ns() {
 // Experiments build: stamp slot `slot` of this CTA's trace record (first writer wins when once == true).
 #define PVA_TRACE(slot)                                                             \
     do {                                                                            \
-        if (kExperiments && tg.trace) tg.trace[(size_t)blockIdx.x * 8 + (slot)] = global_ns(); \
+        if (kExperiments && tg.trace) tg.trace[(size_t)blockIdx.x * kTraceWords + (slot)] = global_ns(); \
+    } while (0)
+// Per-tile stamps of the CTA's thread 0 (group 0, strip 0, the strip's issuing thread): phase 0 tile loop top,
+// 1 staging slot drained, 2 tile landed, 3 strip computed, 4 strip handed to the store engine; first 24 tiles.
+#define PVA_TRACE_TILE(n, phase)                                                                              \
+    do {                                                                                                      \
+        if (kExperiments && tg.trace && tid == 0 && (n) < 24)                                                 \
+            tg.trace[(size_t)blockIdx.x * kTraceWords + 8 + (n) * 5 + (phase)] = global_ns();                  \
     } while (0)
 
 // Source row / column range of a tile, from the same tap formula the consumers use.
@@ -505,15 +513,19 @@ __global__ void __launch_bounds__(kBlockThreads, 1) pva_tiled_kernel(const __gri
         const int rows = max(y_end - y_begin, 0);
         unsigned char* stage_out = out_base + (size_t)strip_it * tg.strip_bytes;
 
+        const int tile_no = (t - t_begin) / tg.groups;  // this group's n-th tile
+        PVA_TRACE_TILE(tile_no, 0);
         if (tg.out_bufs == 1 && tg.bulk_store && in_strip) {
             // single staging buffer: the previous tile's store must have drained it
             if (issuer) bulk_wait_read_all();
             named_bar(bar_strip, strip_threads);
         }
 
+        PVA_TRACE_TILE(tile_no, 1);
         // every thread polls: measured faster than one poller per warp + __syncwarp (43.4 vs 46.0 us)
         mbar_wait(smem_u32(&s_full[2 * s + group]), ph);
         if (tid == 0 && t == t_begin) PVA_TRACE(2);  // first tile landed
+        PVA_TRACE_TILE(tile_no, 2);
 
         if (active_col && rows > 0 && !(dbg & 4)) {
             // staged address of (plane c, source row r, window start) = rowbase[c] + r * W
@@ -643,6 +655,7 @@ __global__ void __launch_bounds__(kBlockThreads, 1) pva_tiled_kernel(const __gri
             }
         }
 
+        PVA_TRACE_TILE(tile_no, 3);
         // this warp no longer reads the input stage
         __syncwarp();
         if ((tid & 31) == 0) mbar_arrive(smem_u32(&s_empty[s]));
@@ -707,6 +720,7 @@ __global__ void __launch_bounds__(kBlockThreads, 1) pva_tiled_kernel(const __gri
                     }
                     bulk_commit();
                 }
+                PVA_TRACE_TILE(tile_no, 4);
                 if (++strip_it >= tg.out_bufs) strip_it = 0;
             } else {
                 // alignment does not allow bulk stores: cooperative element copy by the strip
@@ -957,7 +971,7 @@ cudaError_t launch_tiled(const KParams& p, int out_dtype, int layout, int norm, 
     a.g.l2hint = PVA_KNOB("L2HINT", 3);  // clip bytes are read once, outputs are consumed later: stream both
 #ifdef PVA_EXPERIMENTS
     {
-        // PVA_TILED_TRACE=<hex device address of a uint64 buffer, kMaxGrid * 8 entries per launch>,
+        // PVA_TILED_TRACE=<hex device address of a uint64 buffer, kMaxGrid * 128 entries per launch>,
         // PVA_TILED_TRACE_SLOTS=<launch records the buffer holds>: consecutive launches fill
         // consecutive records (scripts/trace_launch.py)
         static std::atomic<unsigned> launch_no{0};
@@ -966,7 +980,7 @@ cudaError_t launch_tiled(const KParams& p, int out_dtype, int layout, int norm, 
             const unsigned slots = (unsigned)knob_env("PVA_TILED_TRACE_SLOTS", 1);
             const unsigned n = launch_no.fetch_add(1);
             a.g.trace = reinterpret_cast<unsigned long long*>(strtoull(tp, nullptr, 16)) +
-                        (size_t)(n % slots) * kMaxGrid * 8;
+                        (size_t)(n % slots) * kMaxGrid * kTraceWords;
         }
     }
 #endif

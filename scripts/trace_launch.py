@@ -51,7 +51,7 @@ def main():
         sets[i % 4].launch_raw(raw)
     torch.cuda.synchronize()
     n = args.launches
-    trace = torch.zeros((n, KMAXGRID, 8), dtype=torch.int64, device=dev)
+    trace = torch.zeros((n, KMAXGRID, 128), dtype=torch.int64, device=dev)
     os.environ["PVA_TILED_TRACE"] = hex(trace.data_ptr())
     os.environ["PVA_TILED_TRACE_SLOTS"] = str(n)
     torch.cuda.synchronize()
@@ -78,6 +78,23 @@ def main():
             line.append(f"| entry-prev_last_exit {(e0 - prev_exit) / 1e3:6.2f}")
         prev_exit = float(r[:, 6].max())
         print("  ".join(line))
+    # per-tile phases of thread 0 (group 0, strip 0): medians over CTAs and tiles 2..9 of the LAST launch
+    r = tr[order[-1], :grid, 8:128].reshape(grid, 24, 5).double()
+    ok = (r[:, 2:10, :] > 0).all(dim=2)
+    seg = []
+    names2 = ["drain wait (top -> slot free)", "tile wait (slot free -> landed)", "compute (landed -> strip done)",
+              "hand-over (strip done -> store issued)", "loop (store issued -> next top)"]
+    for j in range(4):
+        d = (r[:, 2:10, j + 1] - r[:, 2:10, j])[ok] / 1e3
+        seg.append(d)
+    nxt = (r[:, 3:11, 0] - r[:, 2:10, 4])[ok & (r[:, 3:11, 0] > 0)] / 1e3
+    seg.append(nxt)
+    print("per group-tile phases, us (median / 90th percentile), last launch:")
+    for nm, d in zip(names2, seg):
+        if d.numel():
+            print(f"  {nm:42s} {float(d.median()):6.2f} / {float(d.quantile(0.9)):6.2f}")
+    per = (r[:, 3:11, 0] - r[:, 2:10, 0])[ok & (r[:, 3:11, 0] > 0)] / 1e3
+    print(f"  group-tile period                          {float(per.median()):6.2f} / {float(per.quantile(0.9)):6.2f}")
     torch.save(tr, os.path.join(ROOT, "gpurun_out", "trace.pt"))
 
 
