@@ -479,6 +479,8 @@ def run_b200_arm(args):
     sets, algo_bytes = [], []
     for s in range(n_sets):
         clips = torch.randint(0, 256, (B,) + tuple(shape), dtype=torch.uint8, generator=gen).to(dev)
+        if args.float_clips:
+            clips = clips.float() + 0.25  # float32 samples that are not whole bytes: nothing can be narrowed to uint8
         params = [t.sample_params(shape[2], shape[3]) for _ in range(B)]
         # resident and complete before the timed region; every set has its own outputs, so consecutive
         # launches never share an output buffer (what a prefetching input pipeline's ring looks like)
@@ -487,7 +489,7 @@ def run_b200_arm(args):
         b = 0
         for p in params:
             fh, fw = _lib.source_footprint(shape[2], shape[3], p.oh, p.ow, p.top, p.left, crop)
-            b += C * n_fast * fh * fw + C * (n_fast + n_slow) * crop * crop * esize
+            b += C * n_fast * fh * fw * (4 if args.float_clips else 1) + C * (n_fast + n_slow) * crop * crop * esize
         algo_bytes.append(b)
     stream = torch.cuda.current_stream(dev)
     raw_stream = stream.cuda_stream
@@ -611,7 +613,7 @@ def run_b200_arm(args):
 
     peak, peak_src = measured_peak()
     achieved = mean_algo / (ms_per_step / 1000.0) / 1e9
-    traffic = recorded_traffic(args.workload) if not (args.batch or args.size or args.planar) else None
+    traffic = recorded_traffic(args.workload) if not (args.batch or args.size or args.planar or args.float_clips) else None
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                 "traffic": traffic, "peak_source": peak_src, "frac_of_nominal_8TBs": achieved / NOMINAL_HBM_GBS,
                 "algorithmic_bytes_per_launch": mean_algo,
@@ -844,6 +846,8 @@ def main():
     ap.add_argument("--clock-period", dest="clock_period", type=float, default=0.002)
     ap.add_argument("--serialize-stores", action="store_true",
                     help="do not set PVA_FLAG_OUTPUTS_DISJOINT: every launch waits for the previous one before its first store")
+    ap.add_argument("--float-clips", dest="float_clips", action="store_true",
+                    help="device-resident region on float32 clips (experiments; the e2e leg still uses uint8)")
     ap.add_argument("--planar", action="store_true",
                     help="write the reference's contiguous C x T x S x S order instead of channels-last (experiments)")
     ap.add_argument("--batch", type=int, default=0, help="override the workload's batch (experiments)")

@@ -92,15 +92,16 @@ typedef enum PvaSrcType { PVA_SRC_U8 = 0, PVA_SRC_F32 = 1 } PvaSrcType;
 #define PVA_FLAG_OUTPUTS_DISJOINT 2
 /* Limits: 1..4 channels; n_fast, n_slow <= 128; t_in <= 65535; any h, w, crop.  More than 128 clips
  * or 8 distinct frame_idx tables per call are handled with several launches.  The tiled kernel takes
- * 3-channel uint8 clips, either layout and crops up to 2048; everything else runs on the
+ * 3-channel uint8 or float32 clips, either layout and crops up to 2048; everything else runs on the
  * generic kernel (PVA_KERNEL_AUTO decides; PVA_KERNEL_TILED returns PVA_ERR_UNSUPPORTED instead). */
 
 /*
  * One clip and its per-clip draws.  Replaces the arguments the reference passes implicitly
  * through the op chain of run.py:81-97:
  *   src, t_in, h, w  : the 'video' entry of the sample dict, C x T x H x W, contiguous, in DEVICE
- *                      memory; uint8, or float32 when plan->src_type == PVA_SRC_F32 (generic kernel;
- *                      any float values, evaluated with the reference's two divisions per tap).
+ *                      memory; uint8, or float32 when plan->src_type == PVA_SRC_F32 (any float values;
+ *                      EXACT evaluates them with the reference's two divisions per tap; both kernels
+ *                      take them, the tiled one stages the bands as floats).
  *                      src may also point into PAGE-LOCKED HOST memory that is mapped into the
  *                      device's address space (cudaHostAlloc / cudaHostRegister, a pinned torch
  *                      tensor): the kernel then reads the frames and rows it needs straight over

@@ -93,6 +93,7 @@ struct TileGeom {
     int pdl;         // programmatic dependent launch: 0 off, 1 wait before the first store, 2 wait at the start,
                      // 3 wait only before the CTA exits (PVA_FLAG_OUTPUTS_DISJOINT)
     int tile0_first; // the producer lets a CTA's first tile land before it requests the next ones
+    int src_esz;     // bytes per source sample: 1 (uint8 clips) or 4 (float32 clips, kSrcF32)
     int l2hint;      // bit 0: loads evict_first, bit 1: stores evict_first
     int stages;      // input ring depth (2 or 3)
     int out_bufs;    // staging buffers per strip (2 = double-buffered, 1 = wait before rewriting)
@@ -174,6 +175,11 @@ __device__ __forceinline__ void named_bar(int id, int count) {
 __device__ __forceinline__ uint32_t lds32(uint32_t addr) {
     uint32_t v;
     asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(addr));
+    return v;
+}
+__device__ __forceinline__ float lds_f32(uint32_t addr) {
+    float v;
+    asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(addr));
     return v;
 }
 __device__ __forceinline__ uint32_t lds8(uint32_t addr) {
@@ -293,8 +299,13 @@ __device__ __forceinline__ __half2 bytes_as_half2(uint32_t t) {
 // kNormT: 0 = EXACT, 1 = AFFINE with one scale for all channels (folded into the row table),
 // 2 = AFFINE with per-channel scales.  kPlanar: write C x T x S x S (the reference's order) instead of
 // T x S x S x C.
-template <typename OutT, int kNormT, bool kFastX, bool kPlanar>
+// kSrcF32: the clips hold float32 samples (what pytorchvideo's decoder hands over when a frame is not a
+// whole number of bytes any more): the bands are staged as floats (4x the bytes, so smaller tiles) and
+// the x-pass reads its taps as floats; EXACT evaluates Div255 and Normalize per tap with the reference's
+// two IEEE divisions, AFFINE interpolates the raw values.
+template <typename OutT, int kNormT, bool kFastX, bool kPlanar, bool kSrcF32>
 __global__ void __launch_bounds__(kBlockThreads, 1) pva_tiled_kernel(const __grid_constant__ TiledArgs a) {
+    static_assert(!(kSrcF32 && kFastX), "the aligned-window x-pass is for byte samples");
     extern __shared__ __align__(128) unsigned char smem[];
     constexpr int kNorm = kNormT == 0 ? kNormExact : kNormAffine;
     constexpr bool kUniformNa = kNormT == 1;
@@ -385,10 +396,11 @@ __global__ void __launch_bounds__(kBlockThreads, 1) pva_tiled_kernel(const __gri
                 // One bulk copy per plane: the whole band of source rows, first needed byte (ra, ca)
                 // to last needed byte, rounded out to 16-byte granules.  Rows are contiguous in
                 // memory, so this is a single linear range; staged byte (r, col) sits at
-                //   plane base + (g0 & 15) + (r - ra) * W + (col - ca).
-                const uint8_t* g0 = src + (((size_t)min(lane, 2) * T_in + t_src) * H + ra) * W + ca;
+                //   plane base + (g0 & 15) + ((r - ra) * W + (col - ca)) * bytes-per-sample.
+                const uint32_t esz_src = (uint32_t)tg.src_esz;  // 1 or 4 bytes per sample
+                const uint8_t* g0 = src + ((((size_t)min(lane, 2) * T_in + t_src) * H + ra) * W + ca) * esz_src;
                 const uint32_t sh = (uint32_t)((uintptr_t)g0 & 15);
-                const uint32_t bytes = (sh + (uint32_t)(nrows - 1) * (uint32_t)W + (uint32_t)ncols + 15u) & ~15u;
+                const uint32_t bytes = (sh + ((uint32_t)(nrows - 1) * (uint32_t)W + (uint32_t)ncols) * esz_src + 15u) & ~15u;
                 uint32_t total = lane < 3 ? bytes : 0u;
                 total += __shfl_xor_sync(0xffffffffu, total, 1);
                 total += __shfl_xor_sync(0xffffffffu, total, 2);
@@ -473,7 +485,7 @@ __global__ void __launch_bounds__(kBlockThreads, 1) pva_tiled_kernel(const __gri
             src = g.src, W = g.w, H = g.h, T_in = g.t_in, idx_row = g.idx_row;
             // AFFINE: the row weights absorb the 2^24 of the subnormal trick and, when all
             // channels share it, the normalisation scale 1 / (255 std)
-            const float wscale = (kNorm == kNormAffine) ? 16777216.0f * (kUniformNa ? p.na[0] : 1.0f) : 1.0f;
+            const float wscale = (kNorm == kNormAffine) ? (kSrcF32 ? 1.0f : 16777216.0f) * (kUniformNa ? p.na[0] : 1.0f) : 1.0f;
             for (int i = g_col; i < tg.bands * tg.rps && in_strip; i += strip_threads) {
                 const int y = (i / tg.rps) * tg.R + strip * tg.rps + (i % tg.rps);
                 if (y >= crop) continue;
@@ -541,9 +553,10 @@ __global__ void __launch_bounds__(kBlockThreads, 1) pva_tiled_kernel(const __gri
                 const int t_src = p.frame_idx[idx_row][k];
 #pragma unroll
                 for (int c = 0; c < 3; ++c) {
-                    const uint32_t gc = (uint32_t)(uintptr_t)(src + (((size_t)c * T_in + t_src) * H + ra) * W + ca);
+                    constexpr uint32_t kEsz = kSrcF32 ? 4u : 1u;
+                    const uint32_t gc = (uint32_t)(uintptr_t)(src + ((((size_t)c * T_in + t_src) * H + ra) * W + ca) * kEsz);
                     rowbase[c] = in_base + (uint32_t)s * tg.stage_bytes + (uint32_t)c * tg.plane_stride + (gc & 15u) +
-                                 (uint32_t)(kFastX ? woff : 0) - (uint32_t)ra * (uint32_t)W;
+                                 (uint32_t)(kFastX ? woff : 0) - (uint32_t)ra * (uint32_t)W * kEsz;
                 }
             }
 
@@ -551,11 +564,26 @@ __global__ void __launch_bounds__(kBlockThreads, 1) pva_tiled_kernel(const __gri
             //   EXACT : h = fma(lx0, lut[b0], lx1 * lut[b1])            (ATen's arithmetic)
             //   AFFINE: h = fma(lx1, b1 - b0, b0) * 2^-24               (same value, one rounding)
             auto hrow = [&](int r, float (&h)[kPx][3]) {
-                const uint32_t ro = (uint32_t)r * (uint32_t)W;
+                const uint32_t ro = (uint32_t)r * (uint32_t)W * (kSrcF32 ? 4u : 1u);
 #pragma unroll
                 for (int c = 0; c < 3; ++c) {
                     const uint32_t addr = rowbase[c] + ro;
-                    if (kFastX) {
+                    if constexpr (kSrcF32) {
+                        const float m = p.mean[c], sd = p.std[c];
+#pragma unroll
+                        for (int i = 0; i < kPx; ++i) {
+                            const float f0 = lds_f32(addr + 4u * (uint32_t)off0[i]);
+                            const float f1 = lds_f32(addr + 4u * (uint32_t)off1[i]);
+                            if (kNorm == kNormExact) {
+                                // Div255 then Normalize per tap, true divisions, as the reference ops do (run.py:83-84)
+                                const float v0 = __fdiv_rn(__fdiv_rn(f0, 255.0f) - m, sd);
+                                const float v1 = __fdiv_rn(__fdiv_rn(f1, 255.0f) - m, sd);
+                                h[i][c] = fmaf(lx0[i], v0, lx1[i] * v1);
+                            } else {
+                                h[i][c] = fmaf(lx1[i], f1 - f0, f0);
+                            }
+                        }
+                    } else if (kFastX) {
                         const uint32_t w0 = lds32(addr);
                         const uint32_t w1 = lds32(addr + 4);
                         const uint32_t t0 = __byte_perm(w0, w1, sel0);
@@ -780,10 +808,12 @@ bool plan_tiles(const KParams& p, int out_dtype, int layout, TileGeom* tg, const
         *why = "tiled kernel handles 3-channel clips";
         return false;
     }
-    if (p.src_f32) {
-        *why = "tiled kernel reads uint8 clips";
-        return false;
-    }
+    const int esz_src = p.src_f32 ? 4 : 1;
+    for (int i = 0; i < p.n_clips; ++i)
+        if ((uintptr_t)p.clips[i].src % esz_src) {
+            *why = "float32 clip not 4-byte aligned";
+            return false;
+        }
     const int crop = p.crop;
     const int gx = (crop + kPx - 1) / kPx;
     const int tps = round_up(gx, 32);
@@ -804,12 +834,14 @@ bool plan_tiles(const KParams& p, int out_dtype, int layout, TileGeom* tg, const
 
     // candidate configurations in order of preference:
     // (consumer groups, rows per strip, input stages, staging buffers per strip)
-    static const int kCand[][4] = {{2, 8, 3, 1}, {1, 4, 2, 3}, {1, 4, 3, 2}, {1, 4, 2, 2}, {1, 4, 2, 1}, {1, 2, 3, 2},
+    // {2, 4, 2, 1} is for float32 clips only (their bands are 4x the bytes: 16-row tiles, one stage per group)
+    static const int kCand[][4] = {{2, 8, 3, 1}, {2, 4, 2, 1}, {1, 4, 2, 3}, {1, 4, 3, 2}, {1, 4, 2, 2}, {1, 4, 2, 1}, {1, 2, 3, 2},
                                    {1, 2, 2, 2}, {1, 2, 2, 1}, {1, 1, 2, 2}, {1, 1, 2, 1}};
     const int force_rps = PVA_KNOB("RPS", 0), force_bufs = PVA_KNOB("OUTBUFS", 0),
               force_stages = PVA_KNOB("STAGES", 0), force_groups = PVA_KNOB("GROUPS", 0);
     for (const auto& cand : kCand) {
         const int groups = cand[0], rps = cand[1], stages = cand[2], out_bufs = bulk_ok ? cand[3] : 1;
+        if (groups == 2 && rps == 4 && !p.src_f32) continue;
         if (force_groups && groups != force_groups) continue;
         if (force_rps && rps != force_rps) continue;
         if (force_bufs && cand[3] != force_bufs) continue;
@@ -833,7 +865,7 @@ bool plan_tiles(const KParams& p, int out_dtype, int layout, TileGeom* tg, const
                 host_taps(g.sy, g.top + ye - 1, g.h, &b0, &b1);
                 const int n = b1 - a0 + 1;
                 rows_cap = rows_cap > n ? rows_cap : n;
-                const int bytes = (n - 1) * g.w + ncols;
+                const int bytes = ((n - 1) * g.w + ncols) * esz_src;
                 band_bytes = band_bytes > bytes ? band_bytes : bytes;
             }
         }
@@ -869,6 +901,7 @@ bool plan_tiles(const KParams& p, int out_dtype, int layout, TileGeom* tg, const
         tg->bulk_store = bulk_ok ? 1 : 0;
         tg->total_tiles = p.n_clips * p.n_fast * bands;
         tg->na_uniform = (p.na[0] == p.na[1] && p.na[1] == p.na[2]) ? 1 : 0;
+        tg->src_esz = esz_src;
         tg->debug = PVA_KNOB("DEBUG", 0);
         tg->trace = nullptr;
         return true;
@@ -894,9 +927,9 @@ int sm_count(int dev) {
     return sms;
 }
 
-template <typename OutT, int N, bool F, bool kPlanar>
+template <typename OutT, int N, bool F, bool kPlanar, bool kSrcF32 = false>
 cudaError_t launch_one(const TiledArgs& a, int dev, int grid, int smem, cudaStream_t stream) {
-    auto kern = pva_tiled_kernel<OutT, N, F, kPlanar>;
+    auto kern = pva_tiled_kernel<OutT, N, F, kPlanar, kSrcF32>;
     // The opt-in shared-memory ceiling only ever needs raising (per device, per variant).  This is
     // the one piece of process-wide state the library keeps: a high-water mark per device, updated
     // with relaxed atomics (two threads racing here both make the same idempotent call).
@@ -926,6 +959,12 @@ cudaError_t launch_one(const TiledArgs& a, int dev, int grid, int smem, cudaStre
 
 template <typename OutT, bool kPlanar>
 cudaError_t launch_t(const TiledArgs& a, int norm, bool fastx, int dev, int grid, int smem, cudaStream_t stream) {
+    if (a.p.src_f32) {
+        if (norm == 0) return launch_one<OutT, 0, false, kPlanar, true>(a, dev, grid, smem, stream);
+        if (norm == 1) return launch_one<OutT, 1, false, kPlanar, true>(a, dev, grid, smem, stream);
+        if (norm == 2) return launch_one<OutT, 2, false, kPlanar, true>(a, dev, grid, smem, stream);
+        return cudaErrorInvalidValue;
+    }
 #define PVA_TILED_CASE(N, F) \
     if (norm == N && fastx == F) return launch_one<OutT, N, F, kPlanar>(a, dev, grid, smem, stream);
     PVA_TILED_CASE(0, false)
@@ -954,7 +993,7 @@ cudaError_t launch_tiled(const KParams& p, int out_dtype, int layout, int norm, 
     }
     // the fast x-path needs, for every clip of the launch: up-scaling or identity in x (so that
     // the taps of 4 adjacent outputs fit an aligned 8-byte window) and 4-byte aligned rows
-    bool fastx = true;
+    bool fastx = !p.src_f32;
     for (int i = 0; i < p.n_clips; ++i) {
         const ClipGeom& g = p.clips[i];
         fastx = fastx && (g.w <= g.ow) && (g.w % 4 == 0) && ((uintptr_t)g.src % 4 == 0);

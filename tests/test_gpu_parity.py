@@ -275,10 +275,12 @@ def test_errors_raise_reference_exception_types(cuda_device):
             [torch.zeros(3, 8, 40, 60, dtype=torch.uint8, device="cuda")], [ClipParams(40, 40, 60, 20, 0, False)])
 
 
-def test_float32_frames_like_the_decoder_hands_over(cuda_device):
+@pytest.mark.parametrize("kernel", KERNELS + ["auto"])
+def test_float32_frames_like_the_decoder_hands_over(kernel, cuda_device):
     """pytorchvideo's decoder produces float32 frames in 0..255; the reference ops take them as they
     are.  The float path evaluates Div255/Normalize per tap with true divisions, so EXACT output is
-    bit-identical to the oracle for any float values, integral or not."""
+    bit-identical to the oracle for any float values, integral or not -- on the generic kernel and on the
+    tiled one (which stages the bands as floats); AUTO takes the tiled kernel."""
     kw = full_kwargs(dict(min_short_side_scale=128, max_short_side_scale=160, crop_size=128, num_frames=8,
                           training=True))
     g = torch.Generator().manual_seed(9)
@@ -286,14 +288,43 @@ def test_float32_frames_like_the_decoder_hands_over(cuda_device):
         torch.manual_seed(21)
         draws = pipeline.replay_draws(128, 172, 128, 160, 128, 0.5)
         ref = oracle_explicit(clip, draws, kw)
-        t = pva_b200.make_transform(**kw, out_dtype=torch.float32, channels_last=False, norm_mode="exact")
-        out = t.explicit(clip.cuda(), params_from_draws(draws, 128, 172))
-        assert _lib.last_launch_info()["kernel"] == 1  # float sources take the generic kernel
-        for o, r in zip(out, ref):
-            assert np.abs(o.cpu().numpy() - r.numpy()).max() <= 1e-6  # ATen small-frame wobble
-        t16 = pva_b200.make_transform(**kw)
+        for channels_last in (False, True):
+            t = pva_b200.make_transform(**kw, out_dtype=torch.float32, channels_last=channels_last, norm_mode="exact",
+                                        kernel=kernel)
+            out = t.explicit(clip.cuda(), params_from_draws(draws, 128, 172))
+            assert _lib.last_launch_info()["kernel"] == {"generic": 1, "tiled": 2, "auto": 2}[kernel]
+            for o, r in zip(out, ref):
+                assert np.abs(o.cpu().numpy() - r.numpy()).max() <= 1e-6  # ATen small-frame wobble
+        t16 = pva_b200.make_transform(**kw, kernel=kernel)
         for o, r in zip(t16.explicit(clip.cuda(), params_from_draws(draws, 128, 172)), ref):
             assert np.abs(o.float().cpu().numpy() - r.numpy()).max() <= FP16_TOL
+        t32 = pva_b200.make_transform(**kw, out_dtype=torch.float32, norm_mode="affine", kernel=kernel)
+        for o, r in zip(t32.explicit(clip.cuda(), params_from_draws(draws, 128, 172)), ref):
+            assert np.abs(o.cpu().numpy() - r.numpy()).max() <= AFFINE_FP32_TOL
+
+
+def test_float32_clips_at_full_size_agree_between_the_kernels(cuda_device):
+    """Headline shape with float32 clips that are NOT whole bytes (so nothing can be narrowed to uint8):
+    tiled and generic kernels are two independent implementations of the same arithmetic; EXACT fp32 output
+    must be bit-identical between them, batch of ragged draws, both pathways."""
+    kw = full_kwargs(dict(training=True))
+    g = torch.Generator().manual_seed(31)
+    clips = (torch.rand((2, 3, 64, 256, 340), generator=g) * 255.0).cuda()
+    torch.manual_seed(32)
+    outs = {}
+    for kernel in KERNELS:
+        t = pva_b200.make_transform(**kw, out_dtype=torch.float32, norm_mode="exact", kernel=kernel)
+        if kernel == KERNELS[0]:
+            params = [t.sample_params(256, 340) for _ in range(2)]
+        outs[kernel] = [o.clone() for o in t.run_batch(clips, params)]
+        assert _lib.last_launch_info()["kernel"] == {"generic": 1, "tiled": 2}[kernel]
+    for a, b in zip(outs["generic"], outs["tiled"]):
+        assert torch.equal(a, b)
+    # and against the CPU oracle on one clip
+    p = params[1]
+    ref = oracle_explicit(clips[1].cpu(), (p.size, p.top, p.left, p.flip), kw)
+    for o, r in zip(outs["tiled"], ref):
+        assert np.abs(o[1].cpu().numpy() - r.numpy()).max() <= 1e-6
 
 
 def bench_batch(workload, rank=0):
