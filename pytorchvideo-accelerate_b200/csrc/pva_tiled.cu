@@ -199,12 +199,13 @@ __device__ __forceinline__ unsigned long long global_ns() {
     do {                                                                            \
         if (kExperiments && tg.trace) tg.trace[(size_t)blockIdx.x * kTraceWords + (slot)] = global_ns(); \
     } while (0)
-// Per-tile stamps of the CTA's thread 0 (group 0, strip 0, the strip's issuing thread): phase 0 tile loop top,
-// 1 staging slot drained, 2 tile landed, 3 strip computed, 4 strip handed to the store engine; first 24 tiles.
+// Per-tile stamps of each consumer group's first thread (strip 0's issuing thread): phase 0 tile loop top,
+// 1 staging slot drained, 2 tile landed, 3 strip computed, 4 strip handed to the store engine; the
+// group's tiles 4..15 (steady state), group g at word 8 + g * 60.
 #define PVA_TRACE_TILE(n, phase)                                                                              \
     do {                                                                                                      \
-        if (kExperiments && tg.trace && tid == 0 && (n) < 24)                                                 \
-            tg.trace[(size_t)blockIdx.x * kTraceWords + 8 + (n) * 5 + (phase)] = global_ns();                  \
+        if (kExperiments && tg.trace && gtid == 0 && group < 2 && (n) >= 4 && (n) < 16)                       \
+            tg.trace[(size_t)blockIdx.x * kTraceWords + 8 + group * 60 + ((n) - 4) * 5 + (phase)] = global_ns(); \
     } while (0)
 
 // Source row / column range of a tile, from the same tap formula the consumers use.

@@ -78,23 +78,28 @@ def main():
             line.append(f"| entry-prev_last_exit {(e0 - prev_exit) / 1e3:6.2f}")
         prev_exit = float(r[:, 6].max())
         print("  ".join(line))
-    # per-tile phases of thread 0 (group 0, strip 0): medians over CTAs and tiles 2..9 of the LAST launch
-    r = tr[order[-1], :grid, 8:128].reshape(grid, 24, 5).double()
-    ok = (r[:, 2:10, :] > 0).all(dim=2)
-    seg = []
+    # per-tile phases of each group's first thread: medians over CTAs and the group's tiles 4..15, LAST launch
+    r = tr[order[-1], :grid, 8:128].reshape(grid, 2, 12, 5).double()
     names2 = ["drain wait (top -> slot free)", "tile wait (slot free -> landed)", "compute (landed -> strip done)",
               "hand-over (strip done -> store issued)", "loop (store issued -> next top)"]
-    for j in range(4):
-        d = (r[:, 2:10, j + 1] - r[:, 2:10, j])[ok] / 1e3
-        seg.append(d)
-    nxt = (r[:, 3:11, 0] - r[:, 2:10, 4])[ok & (r[:, 3:11, 0] > 0)] / 1e3
-    seg.append(nxt)
-    print("per group-tile phases, us (median / 90th percentile), last launch:")
-    for nm, d in zip(names2, seg):
-        if d.numel():
-            print(f"  {nm:42s} {float(d.median()):6.2f} / {float(d.quantile(0.9)):6.2f}")
-    per = (r[:, 3:11, 0] - r[:, 2:10, 0])[ok & (r[:, 3:11, 0] > 0)] / 1e3
-    print(f"  group-tile period                          {float(per.median()):6.2f} / {float(per.quantile(0.9)):6.2f}")
+    for g in range(2):
+        rg = r[:, g]
+        ok = (rg[:, 0:11, :] > 0).all(dim=2) & (rg[:, 1:12, 0] > 0)
+        print(f"group {g}: per group-tile phases, us (median / 90th percentile), last launch:")
+        for j in range(4):
+            d = (rg[:, 0:11, j + 1] - rg[:, 0:11, j])[ok] / 1e3
+            if d.numel():
+                print(f"  {names2[j]:42s} {float(d.median()):6.2f} / {float(d.quantile(0.9)):6.2f}   mean {float(d.mean()):5.2f}")
+        d = (rg[:, 1:12, 0] - rg[:, 0:11, 4])[ok] / 1e3
+        print(f"  {names2[4]:42s} {float(d.median()):6.2f} / {float(d.quantile(0.9)):6.2f}   mean {float(d.mean()):5.2f}")
+        per = (rg[:, 1:12, 0] - rg[:, 0:11, 0])[ok] / 1e3
+        print(f"  group-tile period                          {float(per.median()):6.2f} / {float(per.quantile(0.9)):6.2f}   mean {float(per.mean()):5.2f}")
+    # phase of group 1 relative to group 0: (start of group 1's compute - start of group 0's compute) / period
+    both = (r[:, 0, 0:11, 2] > 0) & (r[:, 1, 0:11, 2] > 0) & (r[:, 0, 1:12, 2] > 0)
+    off = ((r[:, 1, 0:11, 2] - r[:, 0, 0:11, 2]) / (r[:, 0, 1:12, 2] - r[:, 0, 0:11, 2]))[both]
+    if off.numel():
+        hist = torch.histc(off.clamp(0, 1).float(), bins=10, min=0, max=1)
+        print("offset of group 1's compute start within group 0's period (deciles):", [int(v) for v in hist.tolist()])
     torch.save(tr, os.path.join(ROOT, "gpurun_out", "trace.pt"))
 
 
