@@ -464,16 +464,32 @@ __global__ void __launch_bounds__(kBlockThreads, 1) pva_tiled_kernel(const __gri
     int strip_it = 0;  // staging buffer index of this strip
     bool may_store = !(tg.pdl == 1 && tg.bulk_store);  // false until griddepcontrol.wait has been executed
 
-    for (int t = t_begin + group; t < t_end; t += tg.groups) {
-        const int it = t - t_begin;
-        const int s = it % n_stages;  // input stage of this tile
-        // its (stage, group) barrier completes once every `period` tiles
-        const int period = (n_stages % tg.groups == 0) ? n_stages : n_stages * tg.groups;
-        const uint32_t ph = (uint32_t)(it / period) & 1u;
-        const int clip_i = t / tiles_per_clip;
-        const int rem = t - clip_i * tiles_per_clip;
-        const int k = rem / tg.bands;
-        const int band = rem - k * tg.bands;
+    // Where this group's tiles are: (clip, frame, band), input stage and barrier phase are carried from
+    // tile to tile instead of being derived from the tile number -- four integer divisions by run-time
+    // values sat on the critical path between one tile's store and the next tile's first instruction.
+    // A (stage, group) barrier completes once every `period` tiles of the CTA.
+    const int period = (n_stages % tg.groups == 0) ? n_stages : n_stages * tg.groups;
+    int clip_i, k, band, s, pc;
+    uint32_t ph;
+    {
+        const int t0 = t_begin + group, it0 = group;
+        clip_i = t0 / tiles_per_clip;
+        const int rem = t0 - clip_i * tiles_per_clip;
+        k = rem / tg.bands;
+        band = rem - k * tg.bands;
+        s = it0 % n_stages;
+        pc = it0 % period;
+        ph = (uint32_t)(it0 / period) & 1u;
+    }
+    for (int t = t_begin + group; t < t_end; t += tg.groups,
+             band += tg.groups, s += tg.groups, pc += tg.groups) {
+        // carry (the step, tg.groups, is at most 2; bands, stages and period are at least 1)
+        while (band >= tg.bands) {
+            band -= tg.bands;
+            if (++k == p.n_fast) k = 0, ++clip_i;
+        }
+        while (s >= n_stages) s -= n_stages;
+        while (pc >= period) pc -= period, ph ^= 1u;
 
         if (clip_i != cur_clip) {
             // A strip rebuilds only ITS OWN rows of the row table (the rows it computes in every band),
