@@ -542,6 +542,30 @@ __global__ void __launch_bounds__(kBlockThreads, 1) pva_tiled_kernel(const __gri
         const int rows = max(y_end - y_begin, 0);
         unsigned char* stage_out = out_base + (size_t)strip_it * tg.strip_bytes;
 
+        // Staged address of (plane c, source row r, window start) = rowbase[c] + r * W.  Worked out BEFORE
+        // the waits below so that its table look-ups and multiplications are not on the path between
+        // "tile has landed" and the first shared-memory load.  Only the low four bits of the global
+        // address matter (the band starts at its 16-byte granule), so 32-bit arithmetic will do.
+        uint32_t rowbase[3];
+        {
+            int ra;  // first source row staged for this tile (row yb of the table belongs to strip 0)
+            {
+                const ClipGeom& g = p.clips[clip_i];
+                int rb;
+                float l0, l1;
+                bilinear_taps(g.sy, g.top + yb, g.h, ra, rb, l0, l1);
+            }
+            const uint32_t t_src = p.frame_idx[idx_row][k];
+            constexpr uint32_t kEsz = kSrcF32 ? 4u : 1u;
+#pragma unroll
+            for (int c = 0; c < 3; ++c) {
+                const uint32_t lin = ((((uint32_t)c * (uint32_t)T_in + t_src) * (uint32_t)H + (uint32_t)ra) * (uint32_t)W + (uint32_t)ca) * kEsz;
+                const uint32_t gc = (uint32_t)(uintptr_t)src + lin;
+                rowbase[c] = in_base + (uint32_t)s * tg.stage_bytes + (uint32_t)c * tg.plane_stride + (gc & 15u) +
+                             (uint32_t)(kFastX ? woff : 0) - (uint32_t)ra * (uint32_t)W * kEsz;
+            }
+        }
+
         const int tile_no = (t - t_begin) / tg.groups;  // this group's n-th tile
         PVA_TRACE_TILE(tile_no, 0);
         if (tg.out_bufs == 1 && tg.bulk_store && in_strip) {
@@ -557,26 +581,6 @@ __global__ void __launch_bounds__(kBlockThreads, 1) pva_tiled_kernel(const __gri
         PVA_TRACE_TILE(tile_no, 2);
 
         if (active_col && rows > 0 && !(dbg & 4)) {
-            // staged address of (plane c, source row r, window start) = rowbase[c] + r * W
-            uint32_t rowbase[3];
-            {
-                int ra;  // first source row staged for this tile (row yb of the table belongs to strip 0)
-                {
-                    const ClipGeom& g = p.clips[clip_i];
-                    int rb;
-                    float l0, l1;
-                    bilinear_taps(g.sy, g.top + yb, g.h, ra, rb, l0, l1);
-                }
-                const int t_src = p.frame_idx[idx_row][k];
-#pragma unroll
-                for (int c = 0; c < 3; ++c) {
-                    constexpr uint32_t kEsz = kSrcF32 ? 4u : 1u;
-                    const uint32_t gc = (uint32_t)(uintptr_t)(src + ((((size_t)c * T_in + t_src) * H + ra) * W + ca) * kEsz);
-                    rowbase[c] = in_base + (uint32_t)s * tg.stage_bytes + (uint32_t)c * tg.plane_stride + (gc & 15u) +
-                                 (uint32_t)(kFastX ? woff : 0) - (uint32_t)ra * (uint32_t)W * kEsz;
-                }
-            }
-
             // x-pass of one source row into h[i][c].
             //   EXACT : h = fma(lx0, lut[b0], lx1 * lut[b1])            (ATen's arithmetic)
             //   AFFINE: h = fma(lx1, b1 - b0, b0) * 2^-24               (same value, one rounding)
