@@ -196,6 +196,12 @@ int pva_preprocess(const PvaClipDesc* clips, int32_t n_clips, const PvaPlan* pla
     kp.fast_clip_elems = (long long)C * plan->n_fast * crop * crop;
     kp.slow_clip_elems = (long long)C * plan->n_slow * crop * crop;
     for (int j = 0; j < plan->n_slow; ++j) kp.slow_idx[j] = (uint16_t)plan->slow_idx[j];
+    for (int k = 0; k < kMaxFrames; ++k) kp.slow_of[k] = kp.slow_next[k] = kNoSlot;
+    for (int j = plan->n_slow - 1; j >= 0; --j) {  // back to front: the chains come out in ascending slot order
+        const int k = plan->slow_idx[j];
+        kp.slow_next[j] = kp.slow_of[k];
+        kp.slow_of[k] = (uint16_t)j;
+    }
     {
         int rc = pva_build_norm_lut(plan->mean, plan->std, C, kp.lut);
         if (rc != PVA_OK) return rc;

@@ -17,6 +17,7 @@ constexpr int kMaxClipsPerLaunch = 128;  // more clips -> the host issues severa
 constexpr int kMaxFrames = 128;          // n_fast limit
 constexpr int kMaxIdxRows = 8;           // distinct temporal index tables per launch
 constexpr int kMaxChannels = 4;
+constexpr uint16_t kNoSlot = 0xffff;
 
 // Geometry of one clip, precomputed on the host (pva_api.cu) from a PvaClipDesc.
 struct ClipGeom {
@@ -46,6 +47,10 @@ struct KParams {
     float lut[kMaxChannels * 256];  // EXACT: ((u / 255) - mean) / std, built on the host
     uint16_t frame_idx[kMaxIdxRows][kMaxFrames];  // UniformTemporalSubsample tables (run.py:82)
     uint16_t slow_idx[kMaxFrames];                // PackPathway table (run.py:59-63)
+    // the same table inverted: first slow slot fed by fast frame k (kNoSlot if none), and the next slot fed
+    // by the same frame (a caller's table may repeat a frame; PackPathway's never does)
+    uint16_t slow_of[kMaxFrames];
+    uint16_t slow_next[kMaxFrames];
     ClipGeom clips[kMaxClipsPerLaunch];
 };
 

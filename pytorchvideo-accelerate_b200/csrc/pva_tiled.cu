@@ -742,12 +742,11 @@ __global__ void __launch_bounds__(kBlockThreads, 1) pva_tiled_kernel(const __gri
                             else bulk_store(d, ssrc + c * sstep, bytes);
                         }
                         if (slow)
-                            for (int j = 0; j < p.n_slow; ++j)
-                                if (p.slow_idx[j] == k) {
-                                    OutT* d = slow + (((size_t)c * p.n_slow + j) * crop + y_begin) * crop;
-                                    if (l2hint & 2) bulk_store_hint(d, ssrc + c * sstep, bytes, pol);
-                                    else bulk_store(d, ssrc + c * sstep, bytes);
-                                }
+                            for (int j = p.slow_of[k]; j != kNoSlot; j = p.slow_next[j]) {
+                                OutT* d = slow + (((size_t)c * p.n_slow + j) * crop + y_begin) * crop;
+                                if (l2hint & 2) bulk_store_hint(d, ssrc + c * sstep, bytes, pol);
+                                else bulk_store(d, ssrc + c * sstep, bytes);
+                            }
                     } else {
                     const uint32_t bytes = (uint32_t)((size_t)rows * crop * 3 * esz);
                     // thread 0 of the strip sends the fast pathway's copy, the first thread of the strip's second
@@ -757,14 +756,13 @@ __global__ void __launch_bounds__(kBlockThreads, 1) pva_tiled_kernel(const __gri
                         const uint64_t pol = l2_evict_first_policy();
                         if (do_fast) bulk_store_hint(fast + ((size_t)k * crop + y_begin) * crop * 3, ssrc, bytes, pol);
                         if (do_slow)
-                            for (int j = 0; j < p.n_slow; ++j)
-                                if (p.slow_idx[j] == k)
-                                    bulk_store_hint(slow + ((size_t)j * crop + y_begin) * crop * 3, ssrc, bytes, pol);
+                            for (int j = p.slow_of[k]; j != kNoSlot; j = p.slow_next[j])
+                                bulk_store_hint(slow + ((size_t)j * crop + y_begin) * crop * 3, ssrc, bytes, pol);
                     } else {
                         if (do_fast) bulk_store(fast + ((size_t)k * crop + y_begin) * crop * 3, ssrc, bytes);
                         if (do_slow)
-                            for (int j = 0; j < p.n_slow; ++j)
-                                if (p.slow_idx[j] == k) bulk_store(slow + ((size_t)j * crop + y_begin) * crop * 3, ssrc, bytes);
+                            for (int j = p.slow_of[k]; j != kNoSlot; j = p.slow_next[j])
+                                bulk_store(slow + ((size_t)j * crop + y_begin) * crop * 3, ssrc, bytes);
                     }
                     }
                     bulk_commit();
@@ -783,16 +781,16 @@ __global__ void __launch_bounds__(kBlockThreads, 1) pva_tiled_kernel(const __gri
                         const OutT v = st[(size_t)c * tg.rps * crop + rem];
                         fast[(((size_t)c * p.n_fast + k) * crop + y_begin) * crop + rem] = v;
                         if (slow)
-                            for (int j = 0; j < p.n_slow; ++j)
-                                if (p.slow_idx[j] == k) slow[(((size_t)c * p.n_slow + j) * crop + y_begin) * crop + rem] = v;
+                            for (int j = p.slow_of[k]; j != kNoSlot; j = p.slow_next[j])
+                                slow[(((size_t)c * p.n_slow + j) * crop + y_begin) * crop + rem] = v;
                     }
                 } else {
                 for (int idx = g_col; idx < n_el; idx += strip_threads) {
                     const OutT v = st[idx];
                     fast[((size_t)k * crop + y_begin) * crop * 3 + idx] = v;
                     if (slow)
-                        for (int j = 0; j < p.n_slow; ++j)
-                            if (p.slow_idx[j] == k) slow[((size_t)j * crop + y_begin) * crop * 3 + idx] = v;
+                        for (int j = p.slow_of[k]; j != kNoSlot; j = p.slow_next[j])
+                            slow[((size_t)j * crop + y_begin) * crop * 3 + idx] = v;
                 }
                 }
                 named_bar(bar_strip, strip_threads);  // staging may be overwritten by the next tile

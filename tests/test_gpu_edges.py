@@ -191,3 +191,24 @@ def test_clip_at_the_edges_of_its_allocation(kernel, cuda_device):
             rs, rf = oracle_clip(clip, p, kw)
             assert np.array_equal(fast[0].cpu().numpy(), rf) and np.array_equal(slow[0].cpu().numpy(), rs)
         del dev, block
+
+
+@pytest.mark.parametrize("kernel", ["generic", "tiled"])
+@pytest.mark.parametrize("channels_last", [True, False])
+def test_slow_table_with_repeated_frames(kernel, channels_last, cuda_device):
+    """PackPathway's table never repeats a frame, but the C ABI takes any slow_idx: a fast frame that
+    feeds several slow slots must be written to each of them (the tiled kernel walks an inverted table)."""
+    from pva_b200.transforms import _IdxTable
+
+    kw = full_kwargs(dict(num_frames=4, slowfast_alpha=2, crop_size=128, min_short_side_scale=128))
+    t = pva_b200.make_transform(**kw, out_dtype=torch.float32, norm_mode="exact", kernel=kernel,
+                                channels_last=channels_last)
+    t.n_slow, t._slow_tab = 5, _IdxTable([0, 0, 3, 1, 3])
+    clip = synth_clip((3, 6, 130, 171), 77)
+    p = t.sample_params(130, 171)
+    slow, fast = t.run_batch([clip.cuda()], [p])
+    torch.cuda.synchronize()
+    assert slow.shape == (1, 3, 5, 128, 128)
+    assert torch.equal(slow[0], fast[0][:, [0, 0, 3, 1, 3]])
+    (rf,) = c_oracle_explicit(clip, (p.size, p.top, p.left, p.flip), dict(kw, is_slowfast=False))
+    assert np.array_equal(fast[0].cpu().numpy(), rf)
