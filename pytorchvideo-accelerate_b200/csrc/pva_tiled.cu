@@ -1,7 +1,8 @@
 // pva_tiled.cu -- the production kernel: persistent, warp-specialised, bulk-copy staged.
 //
 // Work item ("tile") = (clip, fast frame k, band of R output rows), all C=3 channels.
-// One CTA per SM, each with a contiguous share of the tiles.  Per tile:
+// One CTA per SM (on half of the SMs when launches stream, see launch_tiled), each with a contiguous share
+// of the tiles.  Per tile:
 //   producer warp  : one cp.async.bulk (TMA, 1-D) per channel plane over the whole band of source
 //                    rows the tile touches (rows are contiguous, so a band is one linear range),
 //                    into a stage of a 3-deep shared-memory ring; completion on an mbarrier.
@@ -29,6 +30,9 @@
 // (Two column-cropped load paths were built and measured slower on the headline shape -- 128-bit LDGSTS
 // rows, and four tensor maps per clip over the rows of one residue class mod 4; profiles/r1_ablation.md,
 // profiles/r2_ablation.md.  They are no longer in the source.)
+//
+// Launches are chained by programmatic dependent launch; how much of a launch may overlap its predecessor
+// is the caller's call (PVA_FLAG_CLIPS_READY, PVA_FLAG_OUTPUTS_DISJOINT; TileGeom::pdl).
 //
 // Layout: T x S x S x C (channels-last, the default) or the reference's C x T x S x S.  The two differ
 // only in how a strip is staged and stored: one contiguous range of whole output rows, or three
@@ -71,7 +75,7 @@ constexpr int kBlockThreads = kConsumerThreads + 128;
 constexpr int kProducerRegs = 24, kConsumerRegs = 112;
 static_assert(4 * (96 - kProducerRegs) >= 16 * (kConsumerRegs - 96), "consumers would wait forever for registers");
 constexpr int kMaxStages = 3;
-constexpr int kMaxStrips = 8;  // named barriers 1..8 (15 is the consumer-wide one)
+constexpr int kMaxStrips = 8;  // named barriers 1..8, one per strip
 constexpr int kMaxSmem = 227 * 1024;
 constexpr int kPx = 4;  // output columns per thread
 
