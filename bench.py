@@ -832,7 +832,7 @@ def main():
                     help="only the one-process-per-core CPU figure (skip the one-thread and DataLoader modes)")
     ap.add_argument("--overlap-streams", dest="overlap_streams", type=int, default=2,
                     help="also time the K steps issued round-robin on this many streams (informational; 0/1 = skip)")
-    ap.add_argument("--e2e-ctas", dest="e2e_ctas", type=int, default=8,
+    ap.add_argument("--e2e-ctas", dest="e2e_ctas", type=int, default=4,
                     help="grid cap of launches that read pinned host clips in place (PvaPlan.max_ctas)")
     ap.add_argument("--e2e-upload", dest="e2e_upload", choices=["auto", "all", "selected", "inplace"], default="auto",
                     help="e2e H2D leg: whole clips, only the selected frames, or auto (see run_e2e)")

@@ -137,7 +137,7 @@ typedef struct PvaClipDesc {
  *   mean, std        : Normalize (run.py:84)
  *   max_ctas         : 0 = one CTA per SM.  A positive value caps the tiled kernel's grid; meant for
  *                      launches that read their clips from mapped host memory, which are bound by
- *                      PCIe (8 CTAs already saturate it) and should leave the other SMs to whatever
+ *                      PCIe (4 CTAs already saturate it) and should leave the other SMs to whatever
  *                      else runs on the device.  No counterpart in the reference.
  */
 typedef struct PvaPlan {

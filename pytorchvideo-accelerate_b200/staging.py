@@ -86,7 +86,7 @@ class StagedPreprocess:
 
     def __init__(self, transform: GpuClipTransform, batch: int, clip_shape: Sequence[int],
                  device: Optional[torch.device] = None, depth: int = 3, host_out: bool = False,
-                 upload_selected_frames: bool = False, read_in_place: bool = False, max_ctas: int = 8):
+                 upload_selected_frames: bool = False, read_in_place: bool = False, max_ctas: int = 4):
         if depth < 2:
             raise ValueError("depth must be at least 2 to overlap anything")
         self.t = transform

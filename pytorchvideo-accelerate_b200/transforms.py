@@ -438,7 +438,7 @@ class GpuPreprocess:
     """
 
     def __init__(self, transform: GpuClipTransform, device: Union[None, str, torch.device] = None,
-                 upload_selected_frames: bool = False, read_in_place: bool = False, max_ctas: int = 8):
+                 upload_selected_frames: bool = False, read_in_place: bool = False, max_ctas: int = 4):
         self.t = transform
         self.device = torch.device(device) if device is not None else transform.device
         # copy only the frames UniformTemporalSubsample selects (strided DMA, include/pva_preproc.h):
