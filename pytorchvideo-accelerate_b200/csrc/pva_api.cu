@@ -203,9 +203,14 @@ int pva_preprocess(const PvaClipDesc* clips, int32_t n_clips, const PvaPlan* pla
         kp.slow_of[k] = (uint16_t)j;
     }
     {
-        int rc = pva_build_norm_lut(plan->mean, plan->std, C, kp.lut);
-        if (rc != PVA_OK) return rc;
+        // the 256-entry table (768 IEEE divisions) is only read in EXACT mode on uint8 clips
+        if (plan->norm_mode == PVA_NORM_EXACT && plan->src_type == PVA_SRC_U8) {
+            int rc = pva_build_norm_lut(plan->mean, plan->std, C, kp.lut);
+            if (rc != PVA_OK) return rc;
+        }
         for (int c = 0; c < C; ++c) {
+            if (plan->std[c] == 0.0f)
+                return fail(PVA_ERR_INVALID_ARGUMENT, "std evaluated to zero after conversion to float32 (channel %d)", c);
             const double m = (double)plan->mean[c], s = (double)plan->std[c];
             kp.mean[c] = plan->mean[c];
             kp.std[c] = plan->std[c];
