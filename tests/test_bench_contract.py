@@ -42,3 +42,27 @@ def test_clock_sampler_degrades_without_a_gpu():
     off = bench.ClockSampler(0, enabled=False)
     off.mark_start(); off.mark_end()
     assert off.finish()["samples"] == 0
+
+
+def test_staged_outputs_are_views_of_one_buffer():
+    """StagedPreprocess returns [slow, fast] as views of ONE contiguous buffer (one D2H copy per batch):
+    256-byte aligned offsets, no overlap, both memory orders (host side only: no GPU needed)."""
+    import torch
+
+    import pva_b200
+    from pva_b200.staging import _flat_outputs
+
+    for channels_last in (True, False):
+        t = pva_b200.make_transform(training=True, crop_size=100, num_frames=8, slowfast_alpha=4,
+                                    channels_last=channels_last)
+        flat, (slow, fast) = _flat_outputs(t, 3, "cpu", pin=False)
+        want_slow = (3, 2, 100, 100, 3) if channels_last else (3, 3, 2, 100, 100)
+        want_fast = (3, 8, 100, 100, 3) if channels_last else (3, 3, 8, 100, 100)
+        assert tuple(slow.shape) == want_slow and tuple(fast.shape) == want_fast
+        assert slow.dtype == fast.dtype == torch.float16 and slow.is_contiguous() and fast.is_contiguous()
+        o_slow, o_fast = slow.data_ptr() - flat.data_ptr(), fast.data_ptr() - flat.data_ptr()
+        assert o_slow == 0 and o_fast % 256 == 0 and o_fast >= slow.numel() * 2
+        assert o_fast + fast.numel() * 2 <= flat.numel()
+    single = pva_b200.make_transform(is_slowfast=False, num_frames=4, crop_size=64)
+    flat, views = _flat_outputs(single, 2, "cpu", pin=False)
+    assert len(views) == 1 and views[0].data_ptr() == flat.data_ptr()
